@@ -1,0 +1,138 @@
+"""Deterministic synthetic inputs and table-driven full scorers for parity tests and the bench.
+
+There is no network for datasets or checkpoints, so every test / bench input is synthetic
+(BASELINE.md §3).  The neural full scorers of the reference (attention decoder, LM, LLM;
+SURVEY.md §8 a18) are *producers* of ``(n, V)`` log-prob matrices that stay in PyTorch; for
+parity work they are replaced by table look-ups whose output bits are identical on every
+device, so that the reference search (CPU), the oracle (CPU) and the CUDA path see exactly
+the same ``(n, V)`` matrices.
+
+All scorers here implement ``BatchScorerInterface`` (``espnet/nets/scorer_interface.py:83-126``)
+and therefore plug into the unmodified reference ``BatchBeamSearch`` too.
+"""
+
+from typing import Any, List, Tuple
+
+import numpy as np
+import torch
+
+from .scorer_interface import BatchScorerInterface
+
+LOGZERO = -10000000000.0  # espnet/nets/ctc_prefix_score.py:32
+
+
+def prefix_hash(ys: torch.Tensor) -> torch.Tensor:
+    """Integer hash of each int64 prefix row of ``ys (n, L)`` -> ``(n,)`` int64 (exact on any device)."""
+    pos = torch.arange(1, ys.shape[1] + 1, device=ys.device, dtype=torch.int64)
+    mixed = ((ys.to(torch.int64) + 1) * pos) % 1000003
+    return (mixed * 40503).sum(dim=1) % 2147483647
+
+
+class PrefixTableScorer(BatchScorerInterface):
+    """Full scorer whose row is ``table[min(L-1, P-1), hash(prefix) % J]``.
+
+    ``table`` is a ``(P, J, V)`` tensor of log-probabilities fixed in advance, so the
+    scores of a prefix are bit-identical wherever they are computed.
+    """
+
+    def __init__(self, table: torch.Tensor):
+        assert table.dim() == 3
+        self.table = table
+
+    def to(self, device):
+        self.table = self.table.to(device)
+        return self
+
+    def score(self, y, state, x):
+        s, _ = self.batch_score(y.unsqueeze(0), [state], None)
+        return s[0], None
+
+    def batch_score(self, ys: torch.Tensor, states: List[Any], xs: torch.Tensor) -> Tuple[torch.Tensor, List[Any]]:
+        P, J, _ = self.table.shape
+        p = min(ys.shape[1] - 1, P - 1)
+        j = (prefix_hash(ys) % J).to(self.table.device)
+        return self.table[p].index_select(0, j), [None] * ys.shape[0]
+
+
+class SlotTableScorer(BatchScorerInterface):
+    """Full scorer that returns ``tables[step, row0 : row0 + n]`` (positional; the bench workload).
+
+    The matrix a hypothesis sees depends on the decode position and on its slot in the
+    running beam, i.e. ``log_softmax(2*randn(B*W, V))`` with seed 11+step of BASELINE.md §3.
+    """
+
+    def __init__(self, tables: torch.Tensor, row0: int = 0, primer_len: int = 1):
+        assert tables.dim() == 3
+        self.tables = tables
+        self.row0 = row0
+        self.primer_len = primer_len
+
+    def score(self, y, state, x):
+        s, _ = self.batch_score(y.unsqueeze(0), [state], None)
+        return s[0], None
+
+    def batch_score(self, ys, states, xs):
+        step = ys.shape[1] - self.primer_len
+        n = ys.shape[0]
+        return self.tables[step, self.row0 : self.row0 + n], [None] * n
+
+
+class IdentityCTC(torch.nn.Module):
+    """Stand-in for the CTC head (``espnet2/asr/ctc.py:196-204``): the "encoder output" already
+    is the ``(T, V)`` log-posterior matrix, ``log_softmax`` returns a copy of it."""
+
+    def log_softmax(self, hs_pad: torch.Tensor) -> torch.Tensor:
+        return hs_pad.clone()
+
+    def argmax(self, hs_pad: torch.Tensor) -> torch.Tensor:
+        return torch.argmax(hs_pad, dim=2)
+
+
+def random_logp(seed: int, T: int, V: int, scale: float = 3.0) -> torch.Tensor:
+    """``log_softmax(scale * randn(T, V))`` in fp32 on the CPU (BASELINE.md §3 micro-benchmark input)."""
+    g = torch.Generator().manual_seed(seed)
+    return torch.log_softmax(scale * torch.randn(T, V, generator=g), dim=-1)
+
+
+def random_table(seed: int, P: int, J: int, V: int, scale: float = 2.0) -> torch.Tensor:
+    g = torch.Generator().manual_seed(seed)
+    return torch.log_softmax(scale * torch.randn(P, J, V, generator=g), dim=-1)
+
+
+def peaky_case(seed: int, T: int, V: int, ntok: int, eos: int, J: int = 4, sharp: float = 9.0):
+    """A "trained-like" case: a hidden token sequence, CTC posteriors peaked along one
+    alignment of it (blank elsewhere) and a full-scorer table peaked on the same sequence,
+    then on ``eos``.  The search ends by ``end_detect`` after about ``ntok`` positions.
+
+    Returns ``(logp (T, V), table (P, J, V), truth list[int])``.
+    """
+    rng = np.random.default_rng(seed)
+    truth = [int(t) for t in rng.integers(1, V - 1, size=ntok)]
+    truth = [t if t != eos else 1 for t in truth]
+    # alignment: each token gets 1-2 frames, blanks fill the rest
+    frames = np.zeros(T, dtype=np.int64)  # blank = 0
+    slots = np.sort(rng.choice(np.arange(1, T - 1), size=ntok, replace=False))
+    for s, tok in zip(slots, truth):
+        frames[s] = tok
+    g = torch.Generator().manual_seed(seed + 1)
+    logits = torch.randn(T, V, generator=g)
+    logits[torch.arange(T), torch.as_tensor(frames)] += sharp
+    logp = torch.log_softmax(logits, dim=-1)
+    P = ntok + 4
+    tl = 1.5 * torch.randn(P, J, V, generator=g)
+    for p in range(P):
+        tl[p, :, truth[p] if p < ntok else eos] += sharp
+    table = torch.log_softmax(tl, dim=-1)
+    return logp, table, truth
+
+
+__all__ = [
+    "LOGZERO",
+    "prefix_hash",
+    "PrefixTableScorer",
+    "SlotTableScorer",
+    "IdentityCTC",
+    "random_logp",
+    "random_table",
+    "peaky_case",
+]
