@@ -5,3 +5,13 @@ on first use by ``llm_guided_asr_b200._lib`` and its absence is a hard error (no
 """
 
 __version__ = "0.1.0"
+
+from .beam_search import BatchBeamSearch, Hypothesis  # noqa: E402,F401
+from .ctc_prefix_scorer import CTCPrefixScorer  # noqa: E402,F401
+from .length_bonus import LengthBonus  # noqa: E402,F401
+from .scorer_interface import (  # noqa: E402,F401
+    BatchPartialScorerInterface,
+    BatchScorerInterface,
+    PartialScorerInterface,
+    ScorerInterface,
+)

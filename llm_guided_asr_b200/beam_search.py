@@ -1,0 +1,288 @@
+"""Drop-in ``BatchBeamSearch`` whose per-position scoring runs as hand-written sm_100a CUDA.
+
+API mirror of the reference search objects:
+``Hypothesis`` (``espnet/nets/beam_search.py:15-31``), ``BeamSearch.__init__`` (``:37-121``),
+``BeamSearch.forward`` (``:385-498``) and ``BatchBeamSearch`` (``espnet/nets/batch_beam_search.py``):
+same constructor arguments, same call ``beam_search(x=enc (T, D), maxlenratio, minlenratio)``,
+same result (n-best list of ``Hypothesis``, best first), same errors for bad scorers / keys.
+
+What differs is *where* the work happens.  The reference runs, per decode position, ~2 k tiny
+eager ops plus O(beam) device->host syncs.  Here the full scorers
+(attention decoder, LM, LLM - producers of ``(n, V)`` log-prob matrices) still run
+in PyTorch, and everything after them - weighted fusion, pre-beam top-k, the CTC prefix forward
+recursion, global top-k, hypothesis bookkeeping, eos handling and end detection - is two CUDA
+kernels behind the C ABI (``include/lgasr.h``), with one small D2H read per position.
+
+There is no CPU path: construction works anywhere, decoding needs the CUDA library and a GPU.
+"""
+
+from typing import Any, Dict, List, NamedTuple, Optional, Sequence, Union
+
+import torch
+
+from .engine import FusedStepEngine
+from .scorer_interface import BatchScorerInterface, PartialScorerInterface, ScorerInterface
+
+
+class Hypothesis(NamedTuple):
+    """Result type, field-compatible with ``espnet.nets.beam_search.Hypothesis``."""
+
+    yseq: torch.Tensor
+    score: Union[float, torch.Tensor] = 0
+    scores: Dict[str, Union[float, torch.Tensor]] = dict()
+    states: Dict[str, Any] = dict()
+    hs: List[torch.Tensor] = []
+
+    def asdict(self) -> dict:
+        return self._replace(
+            yseq=self.yseq.tolist(),
+            score=float(self.score),
+            scores={k: float(v) for k, v in self.scores.items()},
+        )._asdict()
+
+
+def length_bounds(T: int, maxlenratio: float, minlenratio: float):
+    """maxlen / minlen of ``BeamSearch.forward`` (``beam_search.py:417-427``)."""
+    if maxlenratio == 0:
+        maxlen = T
+    elif maxlenratio < 0:
+        maxlen = -1 * int(maxlenratio)
+    else:
+        maxlen = max(1, int(maxlenratio * T))
+    minlen = -1 * int(minlenratio) if minlenratio < 0 else int(minlenratio * T)
+    return maxlen, minlen
+
+
+class BatchBeamSearch(torch.nn.Module):
+    """Fused batch beam search (one or many utterances in lock-step)."""
+
+    def __init__(
+        self,
+        scorers: Dict[str, ScorerInterface],
+        weights: Dict[str, float],
+        beam_size: int,
+        vocab_size: int,
+        sos: int,
+        eos: int,
+        token_list: List[str] = None,
+        pre_beam_ratio: float = 1.5,
+        pre_beam_score_key: str = None,
+        return_hs: bool = False,
+        hyp_primer: List[int] = None,
+        normalize_length: bool = False,
+    ):
+        super().__init__()
+        self.weights = weights
+        self.scorers = dict()
+        self.full_scorers = dict()
+        self.part_scorers = dict()
+        self.nn_dict = torch.nn.ModuleDict()
+        for k, v in scorers.items():
+            w = weights.get(k, 0)
+            if w == 0 or v is None:  # dropped entirely, beam_search.py:82-85
+                continue
+            assert isinstance(v, ScorerInterface), f"{k} ({type(v)}) does not implement ScorerInterface"
+            self.scorers[k] = v
+            if isinstance(v, PartialScorerInterface):
+                self.part_scorers[k] = v
+            else:
+                self.full_scorers[k] = v
+            if isinstance(v, torch.nn.Module):
+                self.nn_dict[k] = v
+        for k, v in self.full_scorers.items():
+            if not isinstance(v, BatchScorerInterface):
+                raise NotImplementedError(f"full scorer {k} is not a BatchScorerInterface (asr_inference.py:365-380)")
+        if len(self.part_scorers) > 1 or any(not hasattr(v, "ctc") for v in self.part_scorers.values()):
+            raise NotImplementedError("the fused step supports exactly one partial scorer: the CTC prefix scorer")
+        if return_hs:
+            raise NotImplementedError("return_hs is not supported by the fused search")
+        self.sos, self.eos = sos, eos
+        self.hyp_primer = hyp_primer
+        self.token_list = token_list
+        self.pre_beam_size = int(pre_beam_ratio * beam_size)
+        self.beam_size = beam_size
+        self.n_vocab = vocab_size
+        if (
+            pre_beam_score_key is not None
+            and pre_beam_score_key != "full"
+            and pre_beam_score_key not in self.full_scorers
+        ):
+            raise KeyError(f"{pre_beam_score_key} is not found in {self.full_scorers}")
+        self.pre_beam_score_key = pre_beam_score_key
+        self.do_pre_beam = (
+            self.pre_beam_score_key is not None
+            and self.pre_beam_size < self.n_vocab
+            and len(self.part_scorers) > 0
+        )
+        self.return_hs = return_hs
+        self.normalize_length = normalize_length
+        self._engines: Dict[tuple, FusedStepEngine] = {}
+        self.last_steps = 0  # decode positions executed by the last call
+
+    def set_hyp_primer(self, hyp_primer: List[int] = None) -> None:
+        self.hyp_primer = hyp_primer
+
+    # ------------------------------------------------------------------------------------------
+    def _engine(self, B, T, maxcap, primer_len, end_detect, device) -> FusedStepEngine:
+        key = (B, T, maxcap, primer_len, end_detect, str(device))
+        eng = self._engines.get(key)
+        if eng is None:
+            if len(self._engines) >= 4:  # bounded cache of device workspaces
+                _, old = self._engines.popitem()
+                old.close()
+            ctc_name = next(iter(self.part_scorers), None)
+            eng = FusedStepEngine(
+                n_utts=B,
+                max_frames=T,
+                vocab=self.n_vocab,
+                beam=self.beam_size,
+                pre_beam=self.pre_beam_size,
+                term_names=list(self.full_scorers),
+                pre_beam_key=self.pre_beam_score_key,
+                use_ctc=ctc_name is not None,
+                ctc_weight=self.weights[ctc_name] if ctc_name else 0.0,
+                sos=self.sos,
+                eos=self.eos,
+                max_len_cap=maxcap,
+                primer_len=primer_len,
+                end_detect=end_detect,
+                device=device,
+            )
+            self._engines[key] = eng
+        return eng
+
+    def forward(
+        self, x: torch.Tensor, maxlenratio: float = 0.0, minlenratio: float = 0.0, pre_x: torch.Tensor = None
+    ) -> List[Hypothesis]:
+        """One utterance: ``x (T, D)`` encoder output -> n-best ``Hypothesis`` list, best first."""
+        if pre_x is not None:
+            raise NotImplementedError("sequential attention (pre_x) is outside the fused path")
+        return self.decode_batch([x], maxlenratio, minlenratio)[0]
+
+    @torch.no_grad()
+    def decode_batch(
+        self, xs: Sequence[torch.Tensor], maxlenratio: float = 0.0, minlenratio: float = 0.0
+    ) -> List[List[Hypothesis]]:
+        """Many utterances in lock-step: ``xs[b] (T_b, D)``.  Per utterance identical to ``forward``."""
+        B = len(xs)
+        device = xs[0].device
+        if device.type != "cuda":
+            raise RuntimeError("BatchBeamSearch (fused, sm_100a) needs CUDA tensors: there is no CPU fallback")
+        lens = [int(x.shape[0]) for x in xs]
+        T = max(lens)
+        bounds = [length_bounds(t, maxlenratio, minlenratio) for t in lens]
+        maxlen = [b[0] for b in bounds]
+        minlen = [b[1] for b in bounds]
+        primer = [self.sos] if self.hyp_primer is None else list(self.hyp_primer)
+        eng = self._engine(B, T, max(maxlen), len(primer), maxlenratio == 0.0, device)
+        W, V = self.beam_size, self.n_vocab
+
+        # CTCPrefixScorer.batch_init_state: logp = ctc.log_softmax(x[None]) (scorers/ctc.py:96)
+        ctc_name = next(iter(self.part_scorers), None)
+        if ctc_name is not None:
+            ctc = self.part_scorers[ctc_name].ctc
+            logp = torch.zeros(B, T, V, dtype=torch.float32, device=device)
+            for b, x in enumerate(xs):
+                logp[b, : lens[b]] = ctc.log_softmax(x.unsqueeze(0))[0].to(torch.float32)
+            eng.set_posteriors(logp, lens)
+            del logp
+        else:
+            eng.set_posteriors(None, lens)
+        eng.begin(maxlen, minlen, primer)
+
+        names = list(self.full_scorers)
+        wts = [float(self.weights[k]) for k in names]
+        # per-utterance scorer state lists (init_hyp, batch_beam_search.py:142-144)
+        states = {k: [[self.full_scorers[k].batch_init_state(x)] for x in xs] for k in names}
+        n_run = [1] * B
+        done = [0] * B
+        pad = {k: None for k in names}
+        steps = 0
+        for i in range(max(maxlen)):
+            cur_len = len(primer) + i
+            yseq = eng.view(0)  # (B, W, Lcap) current running prefixes
+            mats, consts = [], []
+            new_states = {k: [None] * B for k in names}
+            for k in names:
+                d = self.full_scorers[k]
+                if getattr(d, "constant_score", None) is not None:  # LengthBonus: folded as a scalar term
+                    mats.append(None)
+                    consts.append(float(d.constant_score))
+                    continue
+                if hasattr(d, "batch_score_padded"):  # scorer that fills the padded row layout itself
+                    mats.append(d.batch_score_padded(yseq[:, :, :cur_len], n_run, done))
+                    consts.append(0.0)
+                    continue
+                if B == 1 and not done[0]:
+                    ys = yseq[0, : n_run[0], :cur_len]
+                    sc, st = d.batch_score(ys, states[k][0], xs[0].expand(n_run[0], *xs[0].shape))
+                    new_states[k][0] = st
+                    sc = sc.to(torch.float32)
+                    if sc.stride(-1) != 1 or (sc.shape[0] > 1 and sc.stride(0) < V):
+                        if sc.stride(0) == 0 and sc.stride(-1) == 0:  # constant row (LengthBonus expand)
+                            mats.append(None)
+                            consts.append(float(sc.flatten()[0]))
+                            continue
+                        sc = sc.contiguous()
+                    mats.append(sc)
+                    consts.append(0.0)
+                    continue
+                # generic multi-utterance path: score utterance by utterance, scatter into padded rows
+                if pad[k] is None:
+                    pad[k] = torch.zeros(B * W, V, dtype=torch.float32, device=device)
+                const_val = None
+                for b in range(B):
+                    if done[b] or n_run[b] == 0:
+                        continue
+                    ys = yseq[b, : n_run[b], :cur_len]
+                    sc, st = d.batch_score(ys, states[k][b], xs[b].expand(n_run[b], *xs[b].shape))
+                    new_states[k][b] = st
+                    if sc.stride(0) == 0 and sc.stride(-1) == 0:
+                        const_val = float(sc.flatten()[0])
+                    else:
+                        pad[k][b * W : b * W + n_run[b]] = sc
+                if const_val is not None:
+                    mats.append(None)
+                    consts.append(const_val)
+                else:
+                    mats.append(pad[k])
+                    consts.append(0.0)
+            eng.step(mats, consts, wts)
+            steps += 1
+            nrun_new, done_new, par, _tok, n_active = eng.poll(with_parents=True)
+            # re-order the full scorers' states by the parent slots (batch_beam_search.py:347-351)
+            for k in names:
+                d = self.full_scorers[k]
+                for b in range(B):
+                    if done[b]:
+                        continue
+                    st = new_states[k][b]
+                    states[k][b] = [d.select_state(st, int(par[b, r])) for r in range(int(nrun_new[b]))]
+            n_run = [int(v) for v in nrun_new]
+            done = [int(v) for v in done_new]
+            if n_active == 0:
+                break
+        self.last_steps = steps
+
+        results = []
+        out_names = names + ([ctc_name] if ctc_name is not None else [])
+        for b in range(B):
+            toks, score, scores = eng.gather_ended(b)
+            hyps = [
+                Hypothesis(
+                    yseq=torch.tensor(t, dtype=torch.int64, device=device),
+                    score=torch.tensor(float(score[e]), dtype=torch.float32, device=device),
+                    scores={k: torch.tensor(float(scores[e, j]), device=device) for j, k in enumerate(out_names)},
+                    states={},
+                )
+                for e, t in enumerate(toks)
+            ]
+            if self.normalize_length:  # beam_search.py:452-459 (python's sort is stable)
+                hyps = sorted(hyps, key=lambda h: float(h.score) / (len(h.yseq) - 1), reverse=True)
+            else:
+                hyps = sorted(hyps, key=lambda h: float(h.score), reverse=True)
+            if len(hyps) == 0:  # retry with a smaller minlenratio, beam_search.py:462-471
+                if minlenratio >= 0.1:
+                    hyps = self.decode_batch([xs[b]], maxlenratio, max(0.0, minlenratio - 0.1))[0]
+            results.append(hyps)
+        return results

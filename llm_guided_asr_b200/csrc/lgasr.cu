@@ -1,0 +1,578 @@
+// Host side of the C ABI declared in include/lgasr.h (CUDA runtime only; no torch types).
+#include "../../include/lgasr.h"
+
+#include <atomic>
+#include <climits>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "lgasr_kernels.cuh"
+#include "lgasr_scorer_kernels.cuh"
+
+using namespace lgasr;
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CK(call)                                                                                      \
+  do {                                                                                                \
+    cudaError_t e_ = (call);                                                                          \
+    if (e_ != cudaSuccess) return fail(LGASR_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+#define LAUNCH_CK()                                                                                   \
+  do {                                                                                                \
+    g_launches.fetch_add(1, std::memory_order_relaxed);                                               \
+    cudaError_t e_ = cudaGetLastError();                                                              \
+    if (e_ != cudaSuccess) return fail(LGASR_ECUDA, "%s:%d kernel launch: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+  } while (0)
+
+struct lgasr_handle {
+  lgasr_config cfg;
+  Dev d;
+  int pp, rp, step, begun, have_post;
+  int NL;
+  size_t smem_rows, smem_sel;
+  std::vector<void*> allocs;
+  std::vector<long long> primer;
+  std::vector<int> xlens;
+  int* h_pin;  // pinned staging: n_run[B], done[B]
+  long long* d_primer;
+  float* d_logp_stage;  // staging for set_posteriors_host
+  size_t logp_stage_elems;
+  // host-side replay staging
+  float* term_stage[2][LGASR_MAX_TERMS];
+  size_t term_stage_elems;
+  cudaStream_t copy_stream;
+  cudaEvent_t ev_copy[2], ev_comp[2];
+  // ended-pool cache
+  bool cache_valid;
+  int cache_max_n, cache_steps;
+  std::vector<int> c_n_ended;
+  std::vector<float> c_score, c_scores;
+  std::vector<int4> c_meta;
+  std::vector<int> c_bp_par, c_bp_tok;
+};
+
+template <typename T>
+static int dalloc(lgasr_handle* h, T** p, size_t n) {
+  void* q = nullptr;
+  cudaError_t e = cudaMalloc(&q, n * sizeof(T) + 16);
+  if (e != cudaSuccess) return fail(LGASR_ENOMEM, "cudaMalloc(%zu bytes): %s", n * sizeof(T), cudaGetErrorString(e));
+  h->allocs.push_back(q);
+  *p = reinterpret_cast<T*>(q);
+  return LGASR_OK;
+}
+
+#define TRY(x)            \
+  do {                    \
+    int rc_ = (x);        \
+    if (rc_) return rc_;  \
+  } while (0)
+
+extern "C" int lgasr_version(void) { return LGASR_VERSION; }
+extern "C" const char* lgasr_last_error(void) { return g_err; }
+extern "C" int64_t lgasr_launch_count(void) { return g_launches.load(); }
+
+extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
+  if (!c || !out) return fail(LGASR_EINVAL, "null argument");
+  if (c->n_utts <= 0 || c->max_frames <= 0 || c->vocab <= 1 || c->beam <= 0)
+    return fail(LGASR_EINVAL, "bad extents B=%d T=%d V=%d beam=%d", c->n_utts, c->max_frames, c->vocab, c->beam);
+  if (c->n_terms < 0 || c->n_terms > LGASR_MAX_TERMS) return fail(LGASR_EINVAL, "n_terms %d > %d", c->n_terms, LGASR_MAX_TERMS);
+  if (c->n_terms == 0 && !c->use_ctc) return fail(LGASR_EINVAL, "no scorer at all");
+  if (c->pre_beam_key >= c->n_terms) return fail(LGASR_EINVAL, "pre_beam_key %d out of range", c->pre_beam_key);
+  if (c->eos < 0 || c->eos >= c->vocab || c->blank < 0 || c->blank >= c->vocab) return fail(LGASR_EINVAL, "bad eos/blank");
+  if (c->primer_len < 1 || c->max_len_cap < 1) return fail(LGASR_EINVAL, "bad primer_len/max_len_cap");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(LGASR_ECUDA, "no CUDA device: this library has no CPU fallback");
+
+  lgasr_handle* h = new (std::nothrow) lgasr_handle();
+  if (!h) return fail(LGASR_ENOMEM, "host alloc");
+  h->cfg = *c;
+  Dev& d = h->d;
+  memset(&d, 0, sizeof(d));
+  d.B = c->n_utts;
+  d.T = c->max_frames;
+  d.Tp = (c->max_frames + 3) & ~3;
+  d.V = c->vocab;
+  d.W = c->beam;
+  d.S = c->pre_beam;
+  d.K = c->n_terms;
+  d.key = c->pre_beam_key;
+  d.use_ctc = c->use_ctc ? 1 : 0;
+  d.w_ctc = c->ctc_weight;
+  d.blank = c->blank;
+  d.sos = c->sos;
+  d.eos = c->eos;
+  d.maxlen_cap = c->max_len_cap;
+  d.Lcap = c->primer_len + c->max_len_cap + 1;
+  d.Ecap = c->beam * c->max_len_cap;
+  d.end_detect = c->end_detect ? 1 : 0;
+  d.NS = d.K + d.use_ctc;
+  d.d_end = -10.0;  // float(np.log(1 * np.exp(-10))) == -10.0 exactly, e2e_asr_common.py:17
+  // do_pre_beam rule of beam_search.py:115-119
+  const bool do_pre_beam = d.use_ctc && d.key != -2 && d.S < d.V;
+  d.mode = !d.use_ctc ? kModeNoCtc : (do_pre_beam ? kModePreBeam : kModeFullCtc);
+  if (d.mode == kModePreBeam && d.S < 1) return fail(LGASR_EINVAL, "pre_beam must be >= 1");
+  const int n_sel = d.mode == kModePreBeam ? d.S : d.W;
+  if (n_sel > LGASR_MAX_PREBEAM) {
+    delete h;
+    return fail(LGASR_EINVAL, "selection width %d > %d unsupported", n_sel, LGASR_MAX_PREBEAM);
+  }
+  d.R = d.mode == kModePreBeam ? d.S + 1 : d.W;
+  h->NL = (n_sel + 31) / 32;
+  if (h->NL == 3) h->NL = 4;
+  const int capS = 32 * h->NL;
+  h->smem_rows = (size_t)4 * d.Tp * sizeof(float) + (size_t)kRowWarps * capS * 8 + (size_t)capS * 8;
+  h->smem_sel = (size_t)d.W * d.R * 8 + (size_t)d.W * 8;
+  if (h->smem_rows > 220 * 1024 || h->smem_sel > 220 * 1024) {
+    delete h;
+    return fail(LGASR_EINVAL, "shared memory need too large (T=%d beam=%d)", d.T, d.W);
+  }
+
+  const size_t BW = (size_t)d.B * d.W;
+  int rc = 0;
+  float* xT = nullptr;
+  int* xlen = nullptr;
+  if (d.use_ctc) {
+    rc |= dalloc(h, &xT, (size_t)d.B * d.V * d.Tp);
+    for (int p = 0; p < 2; ++p) rc |= dalloc(h, &d.r[p], BW * 2 * d.Tp);
+  }
+  rc |= dalloc(h, &xlen, d.B);
+  d.xT = xT;
+  d.xlen = xlen;
+  for (int p = 0; p < 2; ++p) {
+    rc |= dalloc(h, &d.s_prev[p], BW);
+    rc |= dalloc(h, &d.score[p], BW);
+    rc |= dalloc(h, &d.scores[p], BW * (d.NS > 0 ? d.NS : 1));
+    rc |= dalloc(h, &d.yseq[p], BW * d.Lcap);
+    rc |= dalloc(h, &d.run_slot[p], BW);
+  }
+  int *maxlen = nullptr, *minlen = nullptr;
+  rc |= dalloc(h, &d.cur_len, d.B);
+  rc |= dalloc(h, &d.n_run, d.B);
+  rc |= dalloc(h, &d.done, d.B);
+  rc |= dalloc(h, &d.step_parent, BW);
+  rc |= dalloc(h, &d.step_tok, BW);
+  rc |= dalloc(h, &maxlen, d.B);
+  rc |= dalloc(h, &minlen, d.B);
+  d.maxlen = maxlen;
+  d.minlen = minlen;
+  rc |= dalloc(h, &d.cand_total, BW * d.R);
+  rc |= dalloc(h, &d.cand_tok, BW * d.R);
+  rc |= dalloc(h, &d.cand_psi, BW * d.R);
+  rc |= dalloc(h, &d.bp_par, (size_t)d.B * d.maxlen_cap * d.W);
+  rc |= dalloc(h, &d.bp_tok, (size_t)d.B * d.maxlen_cap * d.W);
+  rc |= dalloc(h, &d.n_ended, d.B);
+  rc |= dalloc(h, &d.end_score, (size_t)d.B * d.Ecap);
+  rc |= dalloc(h, &d.end_meta, (size_t)d.B * d.Ecap);
+  rc |= dalloc(h, &d.end_scores, (size_t)d.B * d.Ecap * (d.NS > 0 ? d.NS : 1));
+  rc |= dalloc(h, &d.best_by_len, (size_t)d.B * (d.Lcap + 2));
+  rc |= dalloc(h, &d.best_all, d.B);
+  rc |= dalloc(h, &h->d_primer, c->primer_len);
+  if (rc) {
+    lgasr_destroy(h);
+    return LGASR_ENOMEM;
+  }
+  if (cudaMallocHost(&h->h_pin, sizeof(int) * (2 * d.B + 2 * d.B * d.W)) != cudaSuccess) {
+    lgasr_destroy(h);
+    return fail(LGASR_ENOMEM, "cudaMallocHost");
+  }
+  h->xlens.assign(d.B, d.T);
+  h->cache_valid = false;
+
+  // opt in to large dynamic shared memory
+  cudaError_t e = cudaSuccess;
+  switch (h->NL) {
+    case 1: e = cudaFuncSetAttribute(k_score_rows<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
+    case 2: e = cudaFuncSetAttribute(k_score_rows<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
+    default: e = cudaFuncSetAttribute(k_score_rows<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
+  }
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_sel);
+  if (e != cudaSuccess) {
+    lgasr_destroy(h);
+    return fail(LGASR_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  }
+  *out = h;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_destroy(lgasr_handle* h) {
+  if (!h) return LGASR_OK;
+  for (void* p : h->allocs) cudaFree(p);
+  if (h->h_pin) cudaFreeHost(h->h_pin);
+  if (h->d_logp_stage) cudaFree(h->d_logp_stage);
+  for (int s = 0; s < 2; ++s) {
+    for (int k = 0; k < LGASR_MAX_TERMS; ++k)
+      if (h->term_stage[s][k]) cudaFree(h->term_stage[s][k]);
+    if (h->ev_copy[s]) cudaEventDestroy(h->ev_copy[s]);
+    if (h->ev_comp[s]) cudaEventDestroy(h->ev_comp[s]);
+  }
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  delete h;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_set_posteriors(lgasr_handle* h, const float* d_logp, const int32_t* h_xlens, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  cudaStream_t st = (cudaStream_t)stream;
+  Dev& d = h->d;
+  for (int b = 0; b < d.B; ++b) {
+    int l = h_xlens ? h_xlens[b] : d.T;
+    if (l < 1 || l > d.T) return fail(LGASR_EINVAL, "xlens[%d]=%d outside [1,%d]", b, l, d.T);
+    h->xlens[b] = l;
+  }
+  CK(cudaMemcpyAsync(const_cast<int*>(d.xlen), h->xlens.data(), sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
+  if (d.use_ctc) {
+    if (!d_logp) return fail(LGASR_EINVAL, "null posteriors");
+    dim3 grid((d.V + 31) / 32, (d.Tp + 31) / 32, d.B), block(32, 8);
+    k_transpose_pad<<<grid, block, 0, st>>>(d_logp, const_cast<float*>(d.xT), d.xlen, d.T, d.Tp, d.V, d.blank, 0);
+    LAUNCH_CK();
+  }
+  // the host vector is read asynchronously by the copy above: make it safe to modify later
+  CK(cudaStreamSynchronize(st));
+  h->have_post = 1;
+  h->begun = 0;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_set_posteriors_host(lgasr_handle* h, const float* h_logp, const int32_t* h_xlens, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  Dev& d = h->d;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d.use_ctc) {
+    if (!h_logp) return fail(LGASR_EINVAL, "null posteriors");
+    size_t n = (size_t)d.B * d.T * d.V;
+    if (h->logp_stage_elems < n) {
+      if (h->d_logp_stage) cudaFree(h->d_logp_stage);
+      h->d_logp_stage = nullptr;
+      h->logp_stage_elems = 0;
+      if (cudaMalloc(&h->d_logp_stage, n * sizeof(float)) != cudaSuccess) return fail(LGASR_ENOMEM, "stage alloc");
+      h->logp_stage_elems = n;
+    }
+    CK(cudaMemcpyAsync(h->d_logp_stage, h_logp, n * sizeof(float), cudaMemcpyHostToDevice, st));
+  }
+  return lgasr_set_posteriors(h, h->d_logp_stage, h_xlens, stream);
+}
+
+extern "C" int lgasr_begin(lgasr_handle* h, const int32_t* h_maxlen, const int32_t* h_minlen, const int64_t* h_primer,
+                           void* stream) {
+  if (!h || !h_maxlen || !h_minlen || !h_primer) return fail(LGASR_EINVAL, "null argument");
+  if (!h->have_post) return fail(LGASR_ESTATE, "lgasr_begin before lgasr_set_posteriors");
+  cudaStream_t st = (cudaStream_t)stream;
+  Dev& d = h->d;
+  for (int b = 0; b < d.B; ++b)
+    if (h_maxlen[b] > d.maxlen_cap) return fail(LGASR_EINVAL, "maxlen[%d]=%d > cap %d", b, h_maxlen[b], d.maxlen_cap);
+  h->primer.assign(h_primer, h_primer + h->cfg.primer_len);
+  CK(cudaMemcpyAsync(const_cast<int*>(d.maxlen), h_maxlen, sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(const_cast<int*>(d.minlen), h_minlen, sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(h->d_primer, h->primer.data(), sizeof(long long) * h->cfg.primer_len, cudaMemcpyHostToDevice, st));
+  if (d.use_ctc) {
+    const long long n = (long long)d.B * d.W * 2 * d.Tp;
+    k_fill<<<592, 256, 0, st>>>(d.r[0], n, LGASR_LOGZERO);
+    LAUNCH_CK();
+    k_fill<<<592, 256, 0, st>>>(d.r[1], n, LGASR_LOGZERO);
+    LAUNCH_CK();
+    k_ctc_init_state<<<d.B, 32, 0, st>>>(d.xT, d.r[0], d.T, d.Tp, d.V, d.W, d.blank, d.W);
+    LAUNCH_CK();
+  }
+  k_begin<<<d.B, 128, 0, st>>>(d, h->d_primer, h->cfg.primer_len);
+  LAUNCH_CK();
+  CK(cudaStreamSynchronize(st));  // host arrays above may be reused by the caller
+  h->pp = 0;
+  h->rp = 0;
+  h->step = 0;
+  h->begun = 1;
+  h->cache_valid = false;
+  return LGASR_OK;
+}
+
+static int fill_terms(lgasr_handle* h, Terms& tm, const float* const* ptr, const float* cst, const float* w, int64_t ld) {
+  Dev& d = h->d;
+  memset(&tm, 0, sizeof(tm));
+  tm.K = d.K;
+  tm.ld = ld;
+  for (int k = 0; k < d.K; ++k) {
+    tm.ptr[k] = ptr ? ptr[k] : nullptr;
+    tm.cst[k] = cst ? cst[k] : 0.f;
+    tm.w[k] = w ? w[k] : 0.f;
+  }
+  if (d.key >= 0 && !tm.ptr[d.key]) return fail(LGASR_EINVAL, "pre_beam_key term %d has no matrix", d.key);
+  if (ld < d.V && d.K > 0) return fail(LGASR_EINVAL, "ld %lld < V %d", (long long)ld, d.V);
+  return LGASR_OK;
+}
+
+static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st) {
+  Dev& d = h->d;
+  if (h->step >= d.maxlen_cap) return fail(LGASR_ESTATE, "step %d beyond max_len_cap %d", h->step, d.maxlen_cap);
+  dim3 grid(d.W, d.B);
+  switch (h->NL) {
+    case 1: k_score_rows<1><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
+    case 2: k_score_rows<2><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
+    default: k_score_rows<4><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
+  }
+  LAUNCH_CK();
+  k_select<<<d.B, kSelThreads, h->smem_sel, st>>>(d, tm, h->pp, h->step);
+  LAUNCH_CK();
+  h->pp ^= 1;
+  h->rp ^= 1;
+  h->step += 1;
+  h->cache_valid = false;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_step(lgasr_handle* h, const float* const* h_term_ptr, const float* h_term_const,
+                          const float* h_term_weight, int64_t ld, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  if (!h->begun) return fail(LGASR_ESTATE, "lgasr_step before lgasr_begin");
+  Terms tm;
+  TRY(fill_terms(h, tm, h_term_ptr, h_term_const, h_term_weight, ld));
+  return step_impl(h, tm, (cudaStream_t)stream);
+}
+
+extern "C" int lgasr_view(lgasr_handle* h, int which, void** d_ptr, int64_t* ld) {
+  if (!h || !d_ptr) return fail(LGASR_EINVAL, "null argument");
+  Dev& d = h->d;
+  int64_t l = 0;
+  switch (which) {
+    case 0: *d_ptr = d.yseq[h->pp]; l = d.Lcap; break;
+    case 1: *d_ptr = d.n_run; l = 1; break;
+    case 2: *d_ptr = d.step_parent; l = d.W; break;
+    case 3: *d_ptr = d.step_tok; l = d.W; break;
+    case 4: *d_ptr = d.done; l = 1; break;
+    case 5: *d_ptr = d.score[h->pp]; l = d.W; break;
+    case 6: *d_ptr = d.cur_len; l = 1; break;
+    default: return fail(LGASR_EINVAL, "unknown view %d", which);
+  }
+  if (ld) *ld = l;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_poll(lgasr_handle* h, int32_t* h_n_running, int32_t* h_done, int32_t* h_parent, int32_t* h_token,
+                          int32_t* n_active, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  cudaStream_t st = (cudaStream_t)stream;
+  Dev& d = h->d;
+  const int BW = d.B * d.W;
+  int* pin = h->h_pin;
+  CK(cudaMemcpyAsync(pin, d.n_run, sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(pin + d.B, d.done, sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
+  if (h_parent) CK(cudaMemcpyAsync(pin + 2 * d.B, d.step_parent, sizeof(int) * BW, cudaMemcpyDeviceToHost, st));
+  if (h_token) CK(cudaMemcpyAsync(pin + 2 * d.B + BW, d.step_tok, sizeof(int) * BW, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  int act = 0;
+  for (int b = 0; b < d.B; ++b) {
+    if (h_n_running) h_n_running[b] = pin[b];
+    if (h_done) h_done[b] = pin[d.B + b];
+    if (!pin[d.B + b]) ++act;
+  }
+  if (h_parent) memcpy(h_parent, pin + 2 * d.B, sizeof(int) * BW);
+  if (h_token) memcpy(h_token, pin + 2 * d.B + BW, sizeof(int) * BW);
+  if (n_active) *n_active = act;
+  return LGASR_OK;
+}
+
+static int refresh_cache(lgasr_handle* h, cudaStream_t st) {
+  Dev& d = h->d;
+  h->c_n_ended.resize(d.B);
+  CK(cudaMemcpyAsync(h->c_n_ended.data(), d.n_ended, sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  int mx = 0;
+  for (int b = 0; b < d.B; ++b) mx = h->c_n_ended[b] > mx ? h->c_n_ended[b] : mx;
+  const int NS = d.NS > 0 ? d.NS : 1;
+  const int steps = h->step;
+  h->cache_max_n = mx;
+  h->cache_steps = steps;
+  h->c_score.resize((size_t)d.B * (mx ? mx : 1));
+  h->c_meta.resize((size_t)d.B * (mx ? mx : 1));
+  h->c_scores.resize((size_t)d.B * (mx ? mx : 1) * NS);
+  h->c_bp_par.resize((size_t)d.B * (steps ? steps : 1) * d.W);
+  h->c_bp_tok.resize((size_t)d.B * (steps ? steps : 1) * d.W);
+  if (mx > 0) {
+    CK(cudaMemcpy2DAsync(h->c_score.data(), sizeof(float) * mx, d.end_score, sizeof(float) * d.Ecap, sizeof(float) * mx, d.B,
+                         cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(h->c_meta.data(), sizeof(int4) * mx, d.end_meta, sizeof(int4) * d.Ecap, sizeof(int4) * mx, d.B,
+                         cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(h->c_scores.data(), sizeof(float) * mx * NS, d.end_scores, sizeof(float) * d.Ecap * NS,
+                         sizeof(float) * mx * NS, d.B, cudaMemcpyDeviceToHost, st));
+  }
+  if (steps > 0) {
+    CK(cudaMemcpy2DAsync(h->c_bp_par.data(), sizeof(int) * steps * d.W, d.bp_par, sizeof(int) * d.maxlen_cap * d.W,
+                         sizeof(int) * steps * d.W, d.B, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(h->c_bp_tok.data(), sizeof(int) * steps * d.W, d.bp_tok, sizeof(int) * d.maxlen_cap * d.W,
+                         sizeof(int) * steps * d.W, d.B, cudaMemcpyDeviceToHost, st));
+  }
+  CK(cudaStreamSynchronize(st));
+  h->cache_valid = true;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_gather_ended(lgasr_handle* h, int utt, int32_t* n_ended, int32_t* max_len, int64_t* h_tokens,
+                                  int32_t* h_lens, float* h_score, float* h_scores, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  Dev& d = h->d;
+  if (utt < 0 || utt >= d.B) return fail(LGASR_EINVAL, "utt %d out of range", utt);
+  if (!h->begun) return fail(LGASR_ESTATE, "gather before begin");
+  if (!h->cache_valid) TRY(refresh_cache(h, (cudaStream_t)stream));
+  const int n = h->c_n_ended[utt];
+  const int mx = h->cache_max_n, steps = h->cache_steps;
+  const int NS = d.NS > 0 ? d.NS : 1;
+  int ml = 0;
+  for (int e = 0; e < n; ++e) {
+    int l = h->c_meta[(size_t)utt * mx + e].z;
+    ml = l > ml ? l : ml;
+  }
+  if (n_ended) *n_ended = n;
+  if (max_len) *max_len = ml;
+  if (!h_tokens) return LGASR_OK;
+  const int P = h->cfg.primer_len;
+  for (int e = 0; e < n; ++e) {
+    const int4 m = h->c_meta[(size_t)utt * mx + e];  // step, slot, len, extra_eos
+    int64_t* row = h_tokens + (size_t)e * ml;
+    for (int t = 0; t < ml; ++t) row[t] = -1;
+    for (int t = 0; t < P; ++t) row[t] = h->primer[t];
+    int slot = m.y;
+    for (int s = m.x; s >= 0; --s) {
+      if (slot < 0) return fail(LGASR_ESTATE, "broken back-pointer chain (utt %d, ended %d)", utt, e);
+      const size_t o = ((size_t)utt * steps + s) * d.W + slot;
+      row[P + s] = h->c_bp_tok[o];
+      slot = h->c_bp_par[o];
+    }
+    if (m.w) row[P + m.x + 1] = d.eos;
+    if (h_lens) h_lens[e] = m.z;
+    if (h_score) h_score[e] = h->c_score[(size_t)utt * mx + e];
+    if (h_scores)
+      for (int k = 0; k < d.NS; ++k) h_scores[(size_t)e * d.NS + k] = h->c_scores[((size_t)utt * mx + e) * NS + k];
+  }
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_decode_replay(lgasr_handle* h, int n_steps, const float* const* h_term_ptr, const float* h_term_const,
+                                   const float* h_term_weight, int64_t ld, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  if (!h->begun) return fail(LGASR_ESTATE, "replay before begin");
+  const int K = h->d.K;
+  for (int i = 0; i < n_steps; ++i) {
+    Terms tm;
+    TRY(fill_terms(h, tm, h_term_ptr ? h_term_ptr + (size_t)i * K : nullptr, h_term_const, h_term_weight, ld));
+    TRY(step_impl(h, tm, (cudaStream_t)stream));
+  }
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_decode_replay_host(lgasr_handle* h, const float* h_logp, const int32_t* h_xlens, const int32_t* h_maxlen,
+                                        const int32_t* h_minlen, const int64_t* h_primer, int n_steps,
+                                        const float* const* h_term_ptr, const float* h_term_const,
+                                        const float* h_term_weight, int64_t ld, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  Dev& d = h->d;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int K = d.K;
+  const size_t elems = (size_t)d.B * d.W * ld;
+  if (!h->copy_stream) {
+    CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int s = 0; s < 2; ++s) {
+      CK(cudaEventCreateWithFlags(&h->ev_copy[s], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&h->ev_comp[s], cudaEventDisableTiming));
+    }
+  }
+  if (h->term_stage_elems < elems) {
+    for (int s = 0; s < 2; ++s)
+      for (int k = 0; k < LGASR_MAX_TERMS; ++k) {
+        if (h->term_stage[s][k]) cudaFree(h->term_stage[s][k]);
+        h->term_stage[s][k] = nullptr;
+      }
+    h->term_stage_elems = 0;
+    for (int s = 0; s < 2; ++s)
+      for (int k = 0; k < K; ++k)
+        if (cudaMalloc(&h->term_stage[s][k], elems * sizeof(float)) != cudaSuccess) return fail(LGASR_ENOMEM, "term staging");
+    h->term_stage_elems = elems;
+  }
+  // the first matrices travel while the posteriors are transposed
+  auto upload = [&](int i) -> int {
+    const int s = i & 1;
+    if (i >= 2) CK(cudaStreamWaitEvent(h->copy_stream, h->ev_comp[s], 0));
+    for (int k = 0; k < K; ++k) {
+      const float* src = h_term_ptr[(size_t)i * K + k];
+      if (src) CK(cudaMemcpyAsync(h->term_stage[s][k], src, elems * sizeof(float), cudaMemcpyHostToDevice, h->copy_stream));
+    }
+    CK(cudaEventRecord(h->ev_copy[s], h->copy_stream));
+    return LGASR_OK;
+  };
+  TRY(lgasr_set_posteriors_host(h, h_logp, h_xlens, stream));
+  TRY(lgasr_begin(h, h_maxlen, h_minlen, h_primer, stream));
+  if (n_steps > 0) TRY(upload(0));
+  for (int i = 0; i < n_steps; ++i) {
+    const int s = i & 1;
+    if (i + 1 < n_steps) TRY(upload(i + 1));
+    CK(cudaStreamWaitEvent(st, h->ev_copy[s], 0));
+    const float* ptrs[LGASR_MAX_TERMS];
+    for (int k = 0; k < K; ++k) ptrs[k] = h_term_ptr[(size_t)i * K + k] ? h->term_stage[s][k] : nullptr;
+    Terms tm;
+    TRY(fill_terms(h, tm, ptrs, h_term_const, h_term_weight, ld));
+    TRY(step_impl(h, tm, st));
+    CK(cudaEventRecord(h->ev_comp[s], st));
+  }
+  return LGASR_OK;
+}
+
+// ---- stand-alone scorer ABI ---------------------------------------------------------------------
+extern "C" int lgasr_transpose_posteriors(const float* d_logp, int T, int V, int xlen, int blank, float* d_xT, int Tp,
+                                          void* stream) {
+  if (!d_logp || !d_xT || T < 1 || V < 1 || Tp < T) return fail(LGASR_EINVAL, "bad argument");
+  dim3 grid((V + 31) / 32, (Tp + 31) / 32, 1), block(32, 8);
+  k_transpose_pad<<<grid, block, 0, (cudaStream_t)stream>>>(d_logp, d_xT, nullptr, T, Tp, V, blank, xlen);
+  LAUNCH_CK();
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_ctc_initial_state(const float* d_xT, int T, int Tp, int blank, float* d_r0, void* stream) {
+  if (!d_xT || !d_r0 || T < 1 || Tp < T) return fail(LGASR_EINVAL, "bad argument");
+  // V is only used for the per-utterance stride; one utterance here
+  k_ctc_init_state<<<1, 32, 0, (cudaStream_t)stream>>>(d_xT, d_r0, T, Tp, 0, 1, blank, 1);
+  LAUNCH_CK();
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_ctc_prefix_score(const float* d_xT, int T, int Tp, int V, int blank, int eos, int n,
+                                      const float* d_r_prev, const float* d_s_prev, const int32_t* d_last, int olen,
+                                      const int64_t* d_ids, int S, float* d_scores, float* d_log_psi, void* stream) {
+  if (!d_xT || !d_r_prev || !d_last || !d_scores || !d_log_psi || n < 1 || T < 1 || Tp < T)
+    return fail(LGASR_EINVAL, "bad argument");
+  if (S > 0 && !d_ids) return fail(LGASR_EINVAL, "null ids");
+  const size_t smem = (size_t)2 * Tp * sizeof(float);
+  if (smem > 200 * 1024) return fail(LGASR_EINVAL, "T too large");
+  cudaError_t e = cudaFuncSetAttribute(k_ctc_prefix_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+  k_ctc_prefix_score<<<n, 256, smem, (cudaStream_t)stream>>>(d_xT, T, Tp, V, blank, eos, d_r_prev, d_s_prev, d_last, olen,
+                                                            reinterpret_cast<const long long*>(d_ids), S, d_scores, d_log_psi);
+  LAUNCH_CK();
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blank, int m, const float* d_r_prev,
+                                      const int32_t* d_last, const int32_t* d_sel_hyp, const int32_t* d_sel_tok, int olen,
+                                      float* d_r_new, void* stream) {
+  if (!d_xT || !d_r_prev || !d_last || !d_sel_hyp || !d_sel_tok || !d_r_new || m < 1 || T < 1 || Tp < T)
+    return fail(LGASR_EINVAL, "bad argument");
+  const size_t smem = (size_t)4 * Tp * sizeof(float);
+  if (smem > 200 * 1024) return fail(LGASR_EINVAL, "T too large");
+  cudaError_t e = cudaFuncSetAttribute(k_ctc_select_state, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+  k_ctc_select_state<<<m, 32, smem, (cudaStream_t)stream>>>(d_xT, T, Tp, blank, d_r_prev, d_last, d_sel_hyp, d_sel_tok, olen,
+                                                           d_r_new);
+  LAUNCH_CK();
+  return LGASR_OK;
+}

@@ -1,0 +1,563 @@
+// Kernels of the fused step.  Two launches per decode position:
+//
+//   k_score_rows   grid (beam, B): one CTA per running hypothesis
+//                    warp 0      : CTC state of the hypothesis = forward recursion of its parent's
+//                                  state extended by its last token (select_state-on-read), then phi
+//                    warps 1..7  : stream the K full-scorer rows once, fuse sum_k w_k*s_k, keep the
+//                                  pre-beam top-S in registers (no (n,V) temporaries, no topk launch)
+//                    all warps   : log psi of the S candidates (+eos) by warp-shuffle log-sum-exp,
+//                                  + w_ctc*(log psi - s_prev) + running score -> candidate records
+//   k_select       grid (B): global top-beam over the <= beam*(S+1) records of an utterance,
+//                    hypothesis bookkeeping, eos / ended pool, end detection, next yseq column.
+#pragma once
+#include "lgasr_device.cuh"
+
+namespace lgasr {
+
+constexpr int kMaxTerms = 8;
+constexpr int kRowThreads = 256;
+constexpr int kRowWarps = kRowThreads / 32;
+constexpr int kSelThreads = 256;
+
+struct Terms {
+  const float* ptr[kMaxTerms];
+  float cst[kMaxTerms];
+  float w[kMaxTerms];
+  int K;
+  long long ld;
+};
+
+struct Dev {
+  int B, T, Tp, V, W, S, R, K, key, use_ctc, mode, blank, sos, eos, Lcap, Ecap, maxlen_cap, end_detect, NS;
+  float w_ctc;
+  double d_end;
+  const float* xT;  // [B][V][Tp]
+  const int* xlen;  // [B]
+  float* r[2];      // [B][W][2][Tp]
+  float* s_prev[2];
+  float* score[2];
+  float* scores[2];      // [B][W][NS]
+  long long* yseq[2];    // [B][W][Lcap]
+  int* run_slot[2];      // [B][W] slot of a running hyp in the best list of the step that made it
+  int* cur_len;          // [B]
+  int* n_run;            // [B]
+  int* done;             // [B]
+  int* step_parent;      // [B][W]
+  int* step_tok;         // [B][W]
+  const int* maxlen;     // [B]
+  const int* minlen;     // [B]
+  float* cand_total;     // [B][W][R]
+  int* cand_tok;         // [B][W][R]
+  float* cand_psi;       // [B][W][R]
+  int* bp_par;           // [B][maxlen_cap][W]
+  int* bp_tok;           // [B][maxlen_cap][W]
+  int* n_ended;          // [B]
+  float* end_score;      // [B][Ecap]
+  int4* end_meta;        // [B][Ecap]  (step, slot, len, extra_eos)
+  float* end_scores;     // [B][Ecap][NS]
+  float* best_by_len;    // [B][Lcap + 2]
+  float* best_all;       // [B]
+};
+
+// modes
+constexpr int kModePreBeam = 0;  // CTC with pre-beam: S candidates + eos per hypothesis
+constexpr int kModeNoCtc = 1;    // full scorers only: top-beam per hypothesis
+constexpr int kModeFullCtc = 2;  // CTC over the whole vocabulary (ctc_weight == 1.0 / tiny V)
+
+// sum_k w_k * s_k[v] in the reference's fp32 order: ((0 + w0*s0) + w1*s1) + ...  (no FMA contraction)
+__device__ __forceinline__ float fuse_at(const Terms& t, long long rowoff, int v) {
+  float acc = 0.f;
+#pragma unroll
+  for (int k = 0; k < kMaxTerms; ++k) {
+    if (k < t.K) {
+      float s = t.ptr[k] ? __ldg(t.ptr[k] + rowoff + v) : t.cst[k];
+      acc = __fadd_rn(acc, __fmul_rn(t.w[k], s));
+    }
+  }
+  return acc;
+}
+
+__device__ __forceinline__ float4 fuse_at4(const Terms& t, long long rowoff, int v) {
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < kMaxTerms; ++k) {
+    if (k < t.K) {
+      float4 s;
+      if (t.ptr[k])
+        s = __ldcs(reinterpret_cast<const float4*>(t.ptr[k] + rowoff + v));
+      else
+        s = make_float4(t.cst[k], t.cst[k], t.cst[k], t.cst[k]);
+      acc.x = __fadd_rn(acc.x, __fmul_rn(t.w[k], s.x));
+      acc.y = __fadd_rn(acc.y, __fmul_rn(t.w[k], s.y));
+      acc.z = __fadd_rn(acc.z, __fmul_rn(t.w[k], s.z));
+      acc.w = __fadd_rn(acc.w, __fmul_rn(t.w[k], s.w));
+    }
+  }
+  return acc;
+}
+
+// ------------------------------------------------------------------------------------------
+// CTC state of hypothesis (b, h): recursion of the parent's state by the hypothesis' last token
+// (what CTCPrefixScoreTH.__call__ computes for every candidate, ctc_prefix_score.py:122-160, and
+// CTCPrefixScorer.select_state picks, scorers/ctc.py:56-62), done here only for the survivors.
+// One warp.  Shared buffers (Tp floats each): bA, bB, bC, bD.
+// On exit: bA[t] = r_sum[t] (log(r^n + r^b)), bD[t] = r^b[t] of the hypothesis for t in [0, T).
+__device__ __forceinline__ void warp_ctc_state(const float* __restrict__ xT_b,  // [V][Tp] of the utterance
+                                               const float* __restrict__ r_par,  // [2][Tp] parent state (or own)
+                                               float* __restrict__ r_out,        // [2][Tp] own state (written)
+                                               int has_parent, int tok, int par_last, int olen_par, int T, int Tp,
+                                               int blank, float* bA, float* bB, float* bC, float* bD, int lane) {
+  if (!has_parent) {
+    for (int t = lane; t < T; t += 32) {
+      float rn = r_par[t], rb = r_par[Tp + t];
+      r_out[t] = rn;
+      r_out[Tp + t] = rb;
+      bA[t] = lse2(rn, rb);
+      bD[t] = rb;
+    }
+    __syncwarp();
+    return;
+  }
+  const int start = olen_par > 1 ? olen_par : 1;
+  const float* xc = xT_b + (long long)tok * Tp;
+  const float* x0 = xT_b + (long long)blank * Tp;
+  const bool same = (tok == par_last);
+  // phi of the parent, x rows
+  for (int t = lane; t < T; t += 32) {
+    float rn = r_par[t], rb = r_par[Tp + t];
+    bD[t] = same ? rb : lse2(rn, rb);  // phi_prev[t]
+    bA[t] = __ldg(xc + t);
+    bC[t] = __ldg(x0 + t);
+  }
+  __syncwarp();
+  const float rn0 = (olen_par == 0) ? bA[0] : LGASR_LOGZERO;  // r[start-1, 0]  (:128-129)
+  for (int t = start + lane; t < T; t += 32) bB[t] = bD[t - 1] + bA[t];
+  __syncwarp();
+  warp_affine_scan(bA, bB, start, T, rn0, lane);  // bB = r^n
+  __syncwarp();
+  // r^b: a = x0, b[t] = r^n[t-1] + x0[t]
+  for (int t = start + lane; t < T; t += 32) {
+    float prev = (t - 1 >= start) ? bB[t - 1] : rn0;
+    bD[t] = prev + bC[t];
+  }
+  __syncwarp();
+  warp_affine_scan(bC, bD, start, T, LGASR_LOGZERO, lane);  // bD = r^b
+  __syncwarp();
+  for (int t = lane; t < T; t += 32) {
+    float rn, rb;
+    if (t >= start) {
+      rn = bB[t];
+      rb = bD[t];
+    } else if (t == start - 1) {
+      rn = rn0;
+      rb = LGASR_LOGZERO;
+    } else {
+      rn = LGASR_LOGZERO;
+      rb = LGASR_LOGZERO;
+    }
+    r_out[t] = rn;
+    r_out[Tp + t] = rb;
+    bA[t] = lse2(rn, rb);
+    bD[t] = rb;
+  }
+  __syncwarp();
+}
+
+template <int NL>
+__global__ void __launch_bounds__(kRowThreads) k_score_rows(Dev d, Terms tm, int pp, int rp) {
+  const int b = blockIdx.y, h = blockIdx.x;
+  if (d.done[b] || h >= d.n_run[b]) return;
+  extern __shared__ float smem[];
+  const int Tp = d.Tp;
+  float* bA = smem;  // r_sum
+  float* bB = bA + Tp;
+  float* bC = bB + Tp;
+  float* bD = bC + Tp;  // r^b
+  float* m_val = bD + Tp;                              // [kRowWarps][capS]
+  const int capS = 32 * NL;
+  int* m_idx = reinterpret_cast<int*>(m_val + kRowWarps * capS);
+  float* sel_val = reinterpret_cast<float*>(m_idx + kRowWarps * capS);  // [capS]
+  int* sel_tok = reinterpret_cast<int*>(sel_val + capS);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int T = d.xlen[b];
+  const int row = b * d.W + h;
+  const long long rowoff = (long long)row * tm.ld;
+  const int cur_len = d.cur_len[b];
+  const int olen = cur_len - 1;
+  const long long* yrow = d.yseq[pp] + (long long)row * d.Lcap;
+  const int last = (int)yrow[cur_len - 1];
+  const float* xT_b = d.xT + (long long)b * d.V * Tp;
+  const int mode = d.mode;
+  const int n_sel = (mode == kModePreBeam) ? d.S : d.W;
+
+  WarpTop<NL> top;
+  top.init(n_sel);
+
+  const int first_stream_warp = d.use_ctc ? 1 : 0;
+  if (d.use_ctc && warp == 0) {
+    const int par = d.step_parent[row];
+    const int has_parent = par >= 0;
+    const float* r_par = d.r[rp] + ((long long)(b * d.W + (has_parent ? par : h)) * 2) * Tp;
+    float* r_out = d.r[rp ^ 1] + ((long long)row * 2) * Tp;
+    const int par_last = (has_parent && cur_len >= 2) ? (int)yrow[cur_len - 2] : -1;
+    warp_ctc_state(xT_b, r_par, r_out, has_parent, last, par_last, olen - 1, T, Tp, d.blank, bA, bB, bC, bD, lane);
+  } else if (mode != kModeFullCtc) {
+    // ---- stream the fused row, keep the top n_sel --------------------------------------------
+    const int V = d.V;
+    const int nw = kRowWarps - first_stream_warp;
+    const int w = warp - first_stream_warp;
+    bool vec_ok = (tm.ld % 4 == 0) && (d.key < 0 || true);
+#pragma unroll
+    for (int k = 0; k < kMaxTerms; ++k)
+      if (k < tm.K && tm.ptr[k]) vec_ok = vec_ok && ((reinterpret_cast<uintptr_t>(tm.ptr[k]) & 15) == 0);
+    if (vec_ok) {
+      const int nvec = V >> 2;
+      for (int q0 = w * 32; q0 < nvec; q0 += nw * 32) {
+        const int q = q0 + lane;
+        const bool ok = q < nvec;
+        float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) {
+          if (d.key < 0)
+            f = fuse_at4(tm, rowoff, q * 4);
+          else
+            f = __ldcs(reinterpret_cast<const float4*>(tm.ptr[d.key] + rowoff + q * 4));
+        }
+        top.offer(f.x, q * 4 + 0, ok, lane);
+        top.offer(f.y, q * 4 + 1, ok, lane);
+        top.offer(f.z, q * 4 + 2, ok, lane);
+        top.offer(f.w, q * 4 + 3, ok, lane);
+      }
+      // tail
+      for (int v0 = (nvec << 2) + w * 32; v0 < V; v0 += nw * 32) {
+        const int v = v0 + lane;
+        const bool ok = v < V;
+        float f = 0.f;
+        if (ok) f = (d.key < 0) ? fuse_at(tm, rowoff, v) : __ldg(tm.ptr[d.key] + rowoff + v);
+        top.offer(f, v, ok, lane);
+      }
+    } else {
+      for (int v0 = w * 32; v0 < V; v0 += nw * 32) {
+        const int v = v0 + lane;
+        const bool ok = v < V;
+        float f = 0.f;
+        if (ok) f = (d.key < 0) ? fuse_at(tm, rowoff, v) : __ldg(tm.ptr[d.key] + rowoff + v);
+        top.offer(f, v, ok, lane);
+      }
+    }
+  }
+  __syncthreads();
+
+  const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
+  const float hyp_score = d.score[pp][row];
+  const int start = olen > 1 ? olen : 1;
+  const float psi_eos = d.use_ctc ? bA[T - 1] : 0.f;  // r_sum at the end frame (:180-181)
+
+  if (mode == kModeFullCtc) {
+    // ---- CTC over the whole vocabulary: total[v] for every v, keep the top beam ---------------
+    for (int v = warp; v < d.V; v += kRowWarps) {
+      const float* phi = (v == last) ? bD : bA;
+      const float* xr = xT_b + (long long)v * Tp;
+      float rn0 = (olen == 0) ? __ldg(xr) : LGASR_LOGZERO;
+      float psi = warp_prefix_lse(phi, xr, start, T, rn0, lane);
+      if (v == d.eos) psi = psi_eos;
+      if (d.eos != d.blank && v == d.blank) psi = LGASR_LOGZERO;
+      float wfull = fuse_at(tm, rowoff, v);
+      float total = __fadd_rn(__fadd_rn(wfull, __fmul_rn(d.w_ctc, __fsub_rn(psi, s_prev))), hyp_score);
+      if (top.passes(total, v)) top.insert(total, v, lane);
+    }
+  }
+
+  // ---- merge the per-warp lists --------------------------------------------------------------
+  {
+    const bool has_list = (mode == kModeFullCtc) || (warp >= first_stream_warp);
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      m_val[warp * capS + j * 32 + lane] = has_list ? top.v[j] : -INFINITY;
+      m_idx[warp * capS + j * 32 + lane] = has_list ? top.i[j] : 0x7fffffff;
+    }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    WarpTop<NL> fin;
+    fin.init(n_sel);
+    for (int e0 = 0; e0 < kRowWarps * capS; e0 += 32) {
+      float v = m_val[e0 + lane];
+      int i = m_idx[e0 + lane];
+      fin.offer(v, i, i != 0x7fffffff, lane);
+    }
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      sel_val[j * 32 + lane] = fin.v[j];
+      sel_tok[j * 32 + lane] = fin.i[j];
+    }
+  }
+  __syncthreads();
+
+  // ---- candidate records -----------------------------------------------------------------------
+  const int R = d.R;
+  float* c_total = d.cand_total + (long long)row * R;
+  int* c_tok = d.cand_tok + (long long)row * R;
+  float* c_psi = d.cand_psi + (long long)row * R;
+  const int n_rec = (mode == kModePreBeam) ? d.S + 1 : d.W;
+  for (int j = warp; j < n_rec; j += kRowWarps) {
+    int c;
+    bool valid = true;
+    if (j < n_sel) {
+      c = sel_tok[j];
+      if (c == 0x7fffffff) valid = false;  // fewer than n_sel tokens in the vocabulary
+    } else {
+      // eos is always scored by the CTC scorer (:180-181); skip if it already is a candidate
+      c = d.eos;
+      bool dup = false;
+      for (int e = lane; e < n_sel; e += 32) dup |= (sel_tok[e] == c);
+      if (__any_sync(FULLMASK, dup)) valid = false;
+    }
+    float total = -INFINITY, psi = 0.f;
+    if (valid) {
+      const float wfull = fuse_at(tm, rowoff, c);
+      if (d.use_ctc) {
+        const float* phi = (c == last) ? bD : bA;
+        const float* xr = xT_b + (long long)c * Tp;
+        float rn0 = (olen == 0) ? __ldg(xr) : LGASR_LOGZERO;
+        psi = warp_prefix_lse(phi, xr, start, T, rn0, lane);
+        if (c == d.eos) psi = psi_eos;
+        if (d.eos != d.blank && c == d.blank) psi = LGASR_LOGZERO;
+        total = __fadd_rn(__fadd_rn(wfull, __fmul_rn(d.w_ctc, __fsub_rn(psi, s_prev))), hyp_score);
+      } else {
+        total = __fadd_rn(wfull, hyp_score);
+      }
+    }
+    if (lane == 0) {
+      c_total[j] = total;
+      c_tok[j] = valid ? c : -1;
+      c_psi[j] = psi;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp, int step) {
+  const int b = blockIdx.x;
+  if (d.done[b]) return;
+  const int n_run = d.n_run[b];
+  if (n_run <= 0) return;
+  extern __shared__ float smem[];
+  const int R = d.R, W = d.W;
+  const int n_rec_row = (d.mode == kModePreBeam) ? d.S + 1 : d.W;
+  const int nrec = n_run * n_rec_row;
+  float* r_total = smem;                                  // [W*R]
+  int* r_flat = reinterpret_cast<int*>(r_total + W * R);  // [W*R]  h*V + tok  (tie order)
+  int* sel = r_flat + W * R;                              // [W] record index per rank
+  int* dest = sel + W;                                    // [W] >=0 running idx, -1-e ended idx e, INT_MIN dropped
+  __shared__ int sh_nsel, sh_nrun_new, sh_last;
+  const int tid = threadIdx.x;
+
+  for (int e = tid; e < nrec; e += kSelThreads) {
+    int h = e / n_rec_row, j = e - h * n_rec_row;
+    long long o = (long long)(b * W + h) * R + j;
+    int tok = d.cand_tok[o];
+    r_total[e] = d.cand_total[o];
+    r_flat[e] = tok >= 0 ? h * d.V + tok : -1;
+  }
+  if (tid < W) sel[tid] = -1;
+  __syncthreads();
+  // rank by counting
+  for (int e = tid; e < nrec; e += kSelThreads) {
+    int fe = r_flat[e];
+    if (fe < 0) continue;
+    float ve = r_total[e];
+    int rank = 0;
+    for (int o = 0; o < nrec; ++o) {
+      int fo = r_flat[o];
+      if (fo >= 0 && better(r_total[o], fo, ve, fe)) ++rank;
+    }
+    if (rank < W) sel[rank] = e;
+  }
+  __syncthreads();
+
+  const int cur_len = d.cur_len[b];
+  const int maxlen = d.maxlen[b], minlen = d.minlen[b];
+  if (tid == 0) {
+    const bool last = (step == maxlen - 1);
+    int nsel = 0;
+    while (nsel < W && sel[nsel] >= 0) ++nsel;
+    int nrun_new = 0;
+    int n_end = d.n_ended[b];
+    float best_all = d.best_all[b];
+    float* bbl = d.best_by_len + (long long)b * (d.Lcap + 2);
+    const int new_len = cur_len + 1 + (last ? 1 : 0);
+    for (int j = 0; j < nsel; ++j) {
+      int e = sel[j];
+      int tok = r_flat[e] % d.V;
+      bool is_eos = last || tok == d.eos;
+      if (is_eos) {
+        if (step >= minlen && n_end < d.Ecap) {
+          dest[j] = -1 - n_end;
+          float sc = r_total[e];
+          d.end_score[(long long)b * d.Ecap + n_end] = sc;
+          d.end_meta[(long long)b * d.Ecap + n_end] = make_int4(step, j, new_len, last ? 1 : 0);
+          if (sc > best_all) best_all = sc;
+          if (sc > bbl[new_len]) bbl[new_len] = sc;
+          ++n_end;
+        } else {
+          dest[j] = INT_MIN;
+        }
+      } else {
+        dest[j] = nrun_new++;
+      }
+    }
+    d.n_ended[b] = n_end;
+    d.best_all[b] = best_all;
+    // end detection (e2e_asr_common.py:17-48): lengths step, step-1, step-2
+    bool fin = (nrun_new == 0) || last;
+    if (d.end_detect && n_end > 0) {
+      int count = 0;
+      for (int m = 0; m < 3; ++m) {
+        int len = step - m;
+        if (len >= 0 && len <= d.Lcap + 1) {
+          float bs = bbl[len];
+          if (bs > -INFINITY && ((double)bs - (double)best_all) < d.d_end) ++count;
+        }
+      }
+      if (count == 3) fin = true;
+    }
+    d.n_run[b] = nrun_new;
+    d.cur_len[b] = cur_len + 1;
+    if (fin) d.done[b] = 1;
+    sh_nsel = nsel;
+    sh_nrun_new = nrun_new;
+    sh_last = last ? 1 : 0;
+  }
+  __syncthreads();
+  const int nsel = sh_nsel;
+  const int NS = d.NS;
+  // per-hypothesis fields
+  if (tid < nsel) {
+    const int j = tid;
+    const int e = sel[j];
+    const int h = e / n_rec_row, jj = e - h * n_rec_row;
+    const int prow = b * W + h;
+    const long long o = (long long)prow * R + jj;
+    const int tok = d.cand_tok[o];
+    const float total = r_total[e];
+    const float psi = d.cand_psi[o];
+    // trellis
+    const long long bpo = ((long long)b * d.maxlen_cap + step) * W + j;
+    d.bp_par[bpo] = d.run_slot[pp][prow];
+    d.bp_tok[bpo] = tok;
+    const int dj = dest[j];
+    float* sc_out = nullptr;
+    if (dj >= 0) {
+      const int nrow = b * W + dj;
+      d.score[pp ^ 1][nrow] = total;
+      d.s_prev[pp ^ 1][nrow] = psi;
+      d.run_slot[pp ^ 1][nrow] = j;
+      d.step_parent[nrow] = h;
+      d.step_tok[nrow] = tok;
+      sc_out = d.scores[pp ^ 1] + (long long)nrow * NS;
+    } else if (dj != INT_MIN) {
+      sc_out = d.end_scores + ((long long)b * d.Ecap + (-1 - dj)) * NS;
+    }
+    if (sc_out) {
+      const float* sc_in = d.scores[pp] + (long long)prow * NS;
+      const long long rowoff = (long long)prow * tm.ld;
+      for (int k = 0; k < tm.K; ++k) {
+        float s = tm.ptr[k] ? __ldg(tm.ptr[k] + rowoff + tok) : tm.cst[k];
+        sc_out[k] = __fadd_rn(sc_in[k], s);
+      }
+      if (d.use_ctc) sc_out[tm.K] = __fadd_rn(sc_in[tm.K], __fsub_rn(psi, d.s_prev[pp][prow]));
+    }
+  }
+  // next yseq rows of the running hypotheses
+  const int warp = tid >> 5, lane = tid & 31;
+  for (int j = warp; j < nsel; j += kSelThreads / 32) {
+    const int dj = dest[j];
+    if (dj < 0) continue;
+    const int e = sel[j];
+    const int h = e / n_rec_row;
+    const long long* src = d.yseq[pp] + (long long)(b * W + h) * d.Lcap;
+    long long* dst = d.yseq[pp ^ 1] + (long long)(b * W + dj) * d.Lcap;
+    for (int t = lane; t < cur_len; t += 32) dst[t] = src[t];
+    if (lane == 0) dst[cur_len] = (long long)(r_flat[e] % d.V);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// x[B][T][V] -> xT[B][V][Tp] with the padding rule of CTCPrefixScoreTH.__init__ (:46-49)
+__global__ void k_transpose_pad(const float* __restrict__ x, float* __restrict__ xT, const int* __restrict__ xlen,
+                                int T, int Tp, int V, int blank, int xlen_scalar) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int v0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
+  const int len = xlen ? xlen[b] : xlen_scalar;
+  const float* xb = x + (long long)b * T * V;
+  float* xo = xT + (long long)b * V * Tp;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    int t = t0 + i, v = v0 + threadIdx.x;
+    float val = LGASR_LOGZERO;
+    if (v < V) {
+      if (t < len && t < T)
+        val = xb[(long long)t * V + v];
+      else
+        val = (v == blank) ? 0.f : LGASR_LOGZERO;
+    }
+    tile[i][threadIdx.x] = val;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    int v = v0 + i, t = t0 + threadIdx.x;
+    if (v < V && t < Tp) xo[(long long)v * Tp + t] = tile[threadIdx.x][i];
+  }
+}
+
+__global__ void k_fill(float* p, long long n, float v) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    p[i] = v;
+}
+
+// initial CTC state of hypothesis 0 (ctc_prefix_score.py:82-93): r^n = log-zero, r^b = cumsum_t x[t, blank]
+__global__ void k_ctc_init_state(const float* __restrict__ xT, float* __restrict__ r0, int T, int Tp, int V, int W,
+                                 int blank, int per_utt_stride_rows) {
+  const int b = blockIdx.x;
+  const float* x0 = xT + ((long long)b * V + blank) * Tp;
+  float* r = r0 + (long long)b * per_utt_stride_rows * 2 * Tp;
+  if (threadIdx.x == 0) {
+    float acc = 0.f;
+    for (int t = 0; t < T; ++t) {
+      acc = __fadd_rn(acc, x0[t]);
+      r[t] = LGASR_LOGZERO;
+      r[Tp + t] = acc;
+    }
+  }
+}
+
+__global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_len) {
+  const int b = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int W = d.W;
+  if (tid == 0) {
+    d.cur_len[b] = primer_len;
+    d.n_run[b] = 1;
+    d.done[b] = (d.maxlen[b] <= 0) ? 1 : 0;
+    d.n_ended[b] = 0;
+    d.best_all[b] = -INFINITY;
+  }
+  for (int i = tid; i < d.Lcap + 2; i += blockDim.x) d.best_by_len[(long long)b * (d.Lcap + 2) + i] = -INFINITY;
+  for (int i = tid; i < W; i += blockDim.x) {
+    for (int p = 0; p < 2; ++p) {
+      d.score[p][b * W + i] = 0.f;
+      d.s_prev[p][b * W + i] = 0.f;
+      d.run_slot[p][b * W + i] = -1;
+      for (int k = 0; k < d.NS; ++k) d.scores[p][(long long)(b * W + i) * d.NS + k] = 0.f;
+    }
+    d.step_parent[b * W + i] = -1;
+    d.step_tok[b * W + i] = -1;
+  }
+  for (int i = tid; i < primer_len; i += blockDim.x) {
+    d.yseq[0][(long long)(b * W) * d.Lcap + i] = primer[i];
+    d.yseq[1][(long long)(b * W) * d.Lcap + i] = primer[i];
+  }
+}
+
+}  // namespace lgasr

@@ -1,0 +1,153 @@
+"""Drop-in ``CTCPrefixScorer`` (API mirror of ``espnet/nets/scorers/ctc.py:10-157``) on CUDA.
+
+Same constructor and methods as the reference class, so an *unmodified* reference
+``BatchBeamSearch`` (or the non-batch ``BeamSearch``) can drive it through the plug-in API:
+
+* ``batch_init_state(x)``: ``logp = ctc.log_softmax(x[None])`` then the posteriors are re-laid out
+  frames-contiguous on the device (replaces ``CTCPrefixScoreTH.__init__``, ``ctc_prefix_score.py:21-65``)
+* ``batch_score_partial(y, ids, state, x)`` -> ``(scores (n, V), state)``: one kernel computes
+  ``log psi`` of the candidates by warp log-sum-exp (replaces ``CTCPrefixScoreTH.__call__`` ``:67-187``)
+* ``select_state(state, i, new_id)``: the forward recursion of the survivor only (replaces the
+  ``r[:, :, i, idmap[i, new_id]]`` pick, ``scorers/ctc.py:56-62``, of an r tensor the reference
+  materialises for every candidate)
+
+The fused search (``llm_guided_asr_b200.beam_search.BatchBeamSearch``) does not call these methods:
+it only takes ``.ctc`` and ``.eos`` from this object and runs the same device functions inside the
+fused step kernels.  Streaming extension (``extend_prob`` / ``extend_state``) is not implemented yet.
+"""
+
+import ctypes as C
+from typing import Any, List, Tuple
+
+import torch
+
+from . import _lib
+from .scorer_interface import BatchPartialScorerInterface
+
+LOGZERO = -10000000000.0
+
+
+def _st(dev):
+    return int(torch.cuda.current_stream(dev).cuda_stream)
+
+
+class CTCPrefixScorer(BatchPartialScorerInterface):
+    """Decoder interface wrapper for the CUDA CTC prefix scorer."""
+
+    def __init__(self, ctc: torch.nn.Module, eos: int):
+        self.ctc = ctc
+        self.eos = eos
+        self.blank = 0  # scorers/ctc.py:98
+        self.impl = None  # dict with the per-utterance device buffers
+
+    # -- shared ---------------------------------------------------------------------------------
+    def _setup(self, x: torch.Tensor):
+        if not x.is_cuda:
+            raise RuntimeError("CTCPrefixScorer (sm_100a) needs CUDA tensors: there is no CPU fallback")
+        lib = _lib.load()
+        logp = self.ctc.log_softmax(x.unsqueeze(0))[0].to(torch.float32).contiguous()
+        T, V = logp.shape
+        Tp = (T + 3) & ~3
+        xT = torch.empty(V, Tp, dtype=torch.float32, device=x.device)
+        r0 = torch.empty(2, Tp, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(lib.lgasr_transpose_posteriors(logp.data_ptr(), T, V, T, self.blank, xT.data_ptr(), Tp, _st(x.device)))
+            _lib.check(lib.lgasr_ctc_initial_state(xT.data_ptr(), T, Tp, self.blank, r0.data_ptr(), _st(x.device)))
+        self.impl = dict(lib=lib, xT=xT, r0=r0, T=T, Tp=Tp, V=V, device=x.device, dtype=x.dtype)
+
+    def _score(self, last: torch.Tensor, olen: int, r_prev: torch.Tensor, s_prev: torch.Tensor, ids):
+        m = self.impl
+        n = r_prev.shape[0]
+        S = 0 if ids is None else ids.shape[1]
+        scores = torch.empty(n, m["V"], dtype=torch.float32, device=m["device"])
+        log_psi = torch.empty(n, m["V"], dtype=torch.float32, device=m["device"])
+        ids64 = None if ids is None else ids.to(torch.int64).contiguous()
+        with torch.cuda.device(m["device"]):
+            _lib.check(
+                m["lib"].lgasr_ctc_prefix_score(
+                    m["xT"].data_ptr(), m["T"], m["Tp"], m["V"], self.blank, self.eos, n,
+                    r_prev.data_ptr(), s_prev.data_ptr(), last.data_ptr(), olen,
+                    None if ids64 is None else ids64.data_ptr(), S, scores.data_ptr(), log_psi.data_ptr(), _st(m["device"]),
+                )
+            )
+        return scores, log_psi
+
+    def _select(self, r_prev: torch.Tensor, last: torch.Tensor, hyp: torch.Tensor, tok: torch.Tensor, olen: int):
+        m = self.impl
+        k = hyp.shape[0]
+        r_new = torch.empty(k, 2, m["Tp"], dtype=torch.float32, device=m["device"])
+        with torch.cuda.device(m["device"]):
+            _lib.check(
+                m["lib"].lgasr_ctc_select_state(
+                    m["xT"].data_ptr(), m["T"], m["Tp"], self.blank, k, r_prev.data_ptr(), last.data_ptr(),
+                    hyp.data_ptr(), tok.data_ptr(), olen, r_new.data_ptr(), _st(m["device"]),
+                )
+            )
+        return r_new
+
+    # -- batch API (BatchBeamSearch) ------------------------------------------------------------
+    def batch_init_state(self, x: torch.Tensor):
+        self._setup(x)
+        return None
+
+    def batch_score_partial(self, y, ids, state, x):
+        """``y (n, L)`` int64 prefixes, ``ids (n, S)`` int64 candidates or None, ``state`` list of
+        per-hypothesis states (None at the first position).  Returns ``(scores (n, V), batch state)``."""
+        m = self.impl
+        n = len(y)
+        dev = m["device"]
+        olen = len(y[0]) - 1
+        if state is None or state[0] is None:
+            r_prev = m["r0"].unsqueeze(0).expand(n, 2, m["Tp"]).contiguous()
+            s_prev = torch.zeros(n, dtype=torch.float32, device=dev)
+        else:
+            r_prev = torch.stack([s[0] for s in state]).contiguous()
+            s_prev = torch.stack([s[1] for s in state]).to(torch.float32).contiguous()
+        last = torch.as_tensor([int(yi[-1]) for yi in y], dtype=torch.int32, device=dev)
+        scores, log_psi = self._score(last, olen, r_prev, s_prev, ids)
+        return scores.to(m["dtype"]), (r_prev, log_psi, last, olen, "lgasr")
+
+    def select_state(self, state, i, new_id=None):
+        if isinstance(state, list):  # list of per-hypothesis states (batchfy / unbatchfy)
+            return state[i]
+        if type(state) is tuple and len(state) == 5 and state[4] == "lgasr":  # batch state of this class
+            r_prev, log_psi, last, olen, _ = state
+            dev = r_prev.device
+            hyp = torch.as_tensor([int(i)], dtype=torch.int32, device=dev)
+            tok = torch.as_tensor([int(new_id)], dtype=torch.int32, device=dev)
+            r_new = self._select(r_prev, last, hyp, tok, olen)[0]
+            return r_new, log_psi[int(i), int(new_id)]
+        if type(state) is tuple and len(state) == 2 and torch.is_tensor(state[0]) and state[0].dim() > 0:
+            # non-batch API: (scores over the candidate ids, states over the candidate ids)
+            sc, st = state
+            return sc[i], st[i]
+        return None if state is None else state[i]
+
+    # -- non-batch API (BeamSearch) -------------------------------------------------------------
+    def init_state(self, x: torch.Tensor):
+        self._setup(x)
+        return torch.zeros((), dtype=torch.float32, device=x.device), self.impl["r0"]
+
+    def score_partial(self, y, ids, state, x):
+        """1-D prefix ``y``, 1-D candidates ``ids`` -> ``(scores (len(ids),), state)``."""
+        m = self.impl
+        dev = m["device"]
+        prev_score, r_prev = state
+        r_prev = r_prev.reshape(1, 2, m["Tp"]).contiguous()
+        olen = len(y) - 1
+        last = torch.as_tensor([int(y[-1])], dtype=torch.int32, device=dev)
+        ids = ids.to(dev).to(torch.int64).reshape(1, -1)
+        s0 = torch.zeros(1, dtype=torch.float32, device=dev)
+        _, log_psi = self._score(last, olen, r_prev, s0, ids)
+        psi = log_psi[0, ids[0]]
+        S = ids.shape[1]
+        hyp = torch.zeros(S, dtype=torch.int32, device=dev)
+        r_new = self._select(r_prev, last, hyp, ids[0].to(torch.int32).contiguous(), olen)
+        return (psi - prev_score).to(x.dtype), (psi, r_new)
+
+    # -- streaming (next) -------------------------------------------------------
+    def extend_prob(self, x: torch.Tensor):
+        raise NotImplementedError("streaming extend_prob is not implemented in the CUDA scorer yet")
+
+    def extend_state(self, state):
+        raise NotImplementedError("streaming extend_state is not implemented in the CUDA scorer yet")

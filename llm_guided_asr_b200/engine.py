@@ -1,0 +1,248 @@
+"""Thin object wrapper over the C-ABI handle (``include/lgasr.h``): one handle decodes ``B``
+utterances in lock-step.  PyTorch is used for device memory and streams only."""
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _stream_ptr(device) -> int:
+    return int(torch.cuda.current_stream(device).cuda_stream)
+
+
+class FusedStepEngine:
+    """Owns one ``lgasr_handle``.
+
+    Args mirror ``BeamSearch.__init__`` (``espnet/nets/beam_search.py:37-121``) plus batch extents:
+    ``term_names`` are the full scorers in ``self.full_scorers`` order, ``pre_beam_key`` is "full",
+    one of ``term_names`` or None.
+    """
+
+    def __init__(
+        self,
+        n_utts: int,
+        max_frames: int,
+        vocab: int,
+        beam: int,
+        pre_beam: int,
+        term_names: Sequence[str],
+        pre_beam_key: Optional[str],
+        use_ctc: bool,
+        ctc_weight: float,
+        sos: int,
+        eos: int,
+        max_len_cap: int,
+        primer_len: int = 1,
+        end_detect: bool = True,
+        blank: int = 0,
+        device="cuda:0",
+    ):
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _lib.LgasrError("FusedStepEngine needs a CUDA device (no CPU fallback)")
+        self.term_names = list(term_names)
+        if pre_beam_key is None:
+            key = -2
+        elif pre_beam_key == "full":
+            key = -1
+        else:
+            key = self.term_names.index(pre_beam_key)
+        self.cfg = _lib.Config(
+            n_utts=n_utts,
+            max_frames=max_frames,
+            vocab=vocab,
+            beam=beam,
+            pre_beam=pre_beam,
+            n_terms=len(self.term_names),
+            pre_beam_key=key,
+            use_ctc=1 if use_ctc else 0,
+            ctc_weight=float(ctc_weight),
+            blank=blank,
+            sos=sos,
+            eos=eos,
+            max_len_cap=max_len_cap,
+            primer_len=primer_len,
+            end_detect=1 if end_detect else 0,
+        )
+        self.B, self.T, self.V, self.beam = n_utts, max_frames, vocab, beam
+        self.NS = len(self.term_names) + (1 if use_ctc else 0)
+        self.use_ctc = bool(use_ctc)
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.lgasr_create(C.byref(self.cfg), C.byref(self._h)))
+        self._i_nrun = (C.c_int32 * n_utts)()
+        self._i_done = (C.c_int32 * n_utts)()
+        self._i_par = (C.c_int32 * (n_utts * beam))()
+        self._i_tok = (C.c_int32 * (n_utts * beam))()
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self.lib.lgasr_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- CTCPrefixScoreTH.__init__ ------------------------------------------------------------
+    def set_posteriors(self, logp: Optional[torch.Tensor], xlens: Sequence[int]):
+        """``logp (B, T, V)`` fp32 log-posteriors on this device (or on the host), ``xlens[B]``."""
+        xl = _lib.i32_array(xlens)
+        with torch.cuda.device(self.device):
+            st = _stream_ptr(self.device)
+            if logp is None:
+                _lib.check(self.lib.lgasr_set_posteriors(self._h, None, xl, st))
+                return
+            assert logp.dtype == torch.float32 and logp.is_contiguous()
+            assert tuple(logp.shape) == (self.B, self.T, self.V), (tuple(logp.shape), (self.B, self.T, self.V))
+            if logp.is_cuda:
+                _lib.check(self.lib.lgasr_set_posteriors(self._h, logp.data_ptr(), xl, st))
+            else:
+                _lib.check(self.lib.lgasr_set_posteriors_host(self._h, logp.data_ptr(), xl, st))
+
+    def begin(self, maxlen: Sequence[int], minlen: Sequence[int], primer: Sequence[int]):
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.lgasr_begin(
+                    self._h, _lib.i32_array(maxlen), _lib.i32_array(minlen), _lib.i64_array(primer), _stream_ptr(self.device)
+                )
+            )
+
+    def _terms(self, mats, consts, weights):
+        ptrs, ld = [], None
+        for m in mats:
+            if m is None:
+                ptrs.append(0)
+                continue
+            assert m.is_cuda and m.dtype == torch.float32 and m.dim() == 2 and m.stride(1) == 1 and m.shape[1] == self.V
+            ml = m.stride(0) if m.shape[0] > 1 else self.V
+            assert ld is None or ld == ml, "all term matrices must share one row stride"
+            ld = ml
+            ptrs.append(m.data_ptr())
+        return ptrs, (ld if ld is not None else self.V)
+
+    def step(self, mats: List[Optional[torch.Tensor]], consts: List[float], weights: List[float]):
+        """One decode position. ``mats[k]``: ``(B*beam, V)`` fp32 device matrix (row = utt*beam+slot)
+        or None for a constant term ``consts[k]``."""
+        ptrs, ld = self._terms(mats, consts, weights)
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.lgasr_step(
+                    self._h, _lib.ptr_array(ptrs), _lib.f32_array(consts), _lib.f32_array(weights), ld, _stream_ptr(self.device)
+                )
+            )
+
+    def replay(self, mats_per_step, consts, weights, ld=None):
+        """``mats_per_step[i][k]`` device matrices; runs len(mats_per_step) positions without host syncs."""
+        n = len(mats_per_step)
+        flat = []
+        for row in mats_per_step:
+            for m in row:
+                flat.append(0 if m is None else m.data_ptr())
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.lgasr_decode_replay(
+                    self._h, n, _lib.ptr_array(flat), _lib.f32_array(consts), _lib.f32_array(weights), ld or self.V,
+                    _stream_ptr(self.device),
+                )
+            )
+
+    def replay_host(self, logp_host, xlens, maxlen, minlen, primer, mats_per_step_host, consts, weights, ld=None):
+        """Same workload from HOST tensors (pinned for speed): copies inside the call."""
+        n = len(mats_per_step_host)
+        flat = []
+        for row in mats_per_step_host:
+            for m in row:
+                flat.append(0 if m is None else m.data_ptr())
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.lgasr_decode_replay_host(
+                    self._h,
+                    None if logp_host is None else logp_host.data_ptr(),
+                    _lib.i32_array(xlens),
+                    _lib.i32_array(maxlen),
+                    _lib.i32_array(minlen),
+                    _lib.i64_array(primer),
+                    n,
+                    _lib.ptr_array(flat),
+                    _lib.f32_array(consts),
+                    _lib.f32_array(weights),
+                    ld or self.V,
+                    _stream_ptr(self.device),
+                )
+            )
+
+    def poll(self, with_parents=True):
+        """(n_running[B], done[B], parent[B][beam], token[B][beam], n_active) as numpy / int."""
+        act = C.c_int32()
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.lgasr_poll(
+                    self._h,
+                    self._i_nrun,
+                    self._i_done,
+                    self._i_par if with_parents else None,
+                    self._i_tok if with_parents else None,
+                    C.byref(act),
+                    _stream_ptr(self.device),
+                )
+            )
+        nrun = np.ctypeslib.as_array(self._i_nrun).copy()
+        done = np.ctypeslib.as_array(self._i_done).copy()
+        par = tok = None
+        if with_parents:
+            par = np.ctypeslib.as_array(self._i_par).reshape(self.B, self.beam).copy()
+            tok = np.ctypeslib.as_array(self._i_tok).reshape(self.B, self.beam).copy()
+        return nrun, done, par, tok, int(act.value)
+
+    def view(self, which: int) -> torch.Tensor:
+        """Zero-copy device tensors: 0 yseq (B, beam, Lcap) int64, 1 n_running, 2 parent, 3 token,
+        4 done, 5 score, 6 cur_len."""
+        p, ld = C.c_void_p(), C.c_int64()
+        _lib.check(self.lib.lgasr_view(self._h, which, C.byref(p), C.byref(ld)))
+        B, W = self.B, self.beam
+        shape, ts = {
+            0: ((B, W, int(ld.value)), "<i8"),
+            1: ((B,), "<i4"),
+            2: ((B, W), "<i4"),
+            3: ((B, W), "<i4"),
+            4: ((B,), "<i4"),
+            5: ((B, W), "<f4"),
+            6: ((B,), "<i4"),
+        }[which]
+        return torch.as_tensor(_lib.DeviceView(p.value, shape, ts), device=self.device)
+
+    def gather_ended(self, utt: int):
+        """All ended hypotheses of ``utt`` in ending order: (tokens list[list[int]], score (n,), scores (n, NS))."""
+        n, ml = C.c_int32(), C.c_int32()
+        with torch.cuda.device(self.device):
+            st = _stream_ptr(self.device)
+            _lib.check(self.lib.lgasr_gather_ended(self._h, utt, C.byref(n), C.byref(ml), None, None, None, None, st))
+            n, ml = int(n.value), int(ml.value)
+            if n == 0:
+                return [], np.zeros((0,), np.float32), np.zeros((0, self.NS), np.float32)
+            toks = np.empty((n, ml), np.int64)
+            lens = np.empty((n,), np.int32)
+            score = np.empty((n,), np.float32)
+            scores = np.empty((n, max(self.NS, 1)), np.float32)
+            _lib.check(
+                self.lib.lgasr_gather_ended(
+                    self._h,
+                    utt,
+                    None,
+                    None,
+                    toks.ctypes.data_as(_lib._PI64),
+                    lens.ctypes.data_as(_lib._PI32),
+                    score.ctypes.data_as(_lib._PF),
+                    scores.ctypes.data_as(_lib._PF),
+                    st,
+                )
+            )
+        return [toks[i, : lens[i]].tolist() for i in range(n)], score, scores[:, : self.NS]

@@ -1,0 +1,82 @@
+"""GPU parity: the fused CUDA search (through the C ABI) against the reference's own n-best lists
+(tests/golden/*.npz, recorded from the unmodified reference) and against the oracle.
+
+Bar (BASELINE.json north_star): token sequences bit-exact, hypothesis scores within 1e-4 abs (fp32).
+"""
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import GOLDEN_NAMES, SCORE_ATOL, Golden, oracle_from_golden, torch_scorers
+
+pytestmark = pytest.mark.gpu
+
+
+def build_search(g, device):
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer, LengthBonus
+    from llm_guided_asr_b200 import synthetic as syn
+
+    c = g.spec
+    dec, lm, V = torch_scorers(g, device)
+    scorers = dict(
+        decoder=dec,
+        ctc=CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=c["eos"]),
+        length_bonus=LengthBonus(V),
+        lm=lm,
+    )
+    return BatchBeamSearch(
+        scorers=scorers,
+        weights=g.weights,
+        beam_size=c["beam"],
+        vocab_size=V,
+        sos=c["sos"],
+        eos=c["eos"],
+        pre_beam_score_key=c["key"],
+        normalize_length=c.get("norm", False),
+        hyp_primer=c.get("primer"),
+    )
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_fused_search_matches_reference_golden(name):
+    g = Golden(name)
+    c = g.spec
+    dev = torch.device("cuda:0")
+    bs = build_search(g, dev)
+    x = torch.from_numpy(g["logp"]).to(dev)
+    nbest = bs(x=x, maxlenratio=c["maxr"], minlenratio=c["minr"])
+    ref = g.nbest()
+    assert bs.last_steps == int(g["n_steps"])
+    assert len(nbest) == len(ref)
+    for h, (yseq, score) in zip(nbest, ref):
+        assert h.yseq.tolist() == yseq
+        assert abs(float(h.score) - score) <= SCORE_ATOL, (float(h.score), score)
+    for k in c["names"]:
+        got = np.array([float(h.scores[k]) for h in nbest], dtype=np.float32)
+        np.testing.assert_allclose(got, g[f"nbest_scores_{k}"], atol=2 * SCORE_ATOL, rtol=1e-6)
+
+
+def test_decode_batch_equals_single_and_oracle():
+    """Several goldens of one shape decoded in lock-step == each decoded alone == the oracle."""
+    names = ["key_decoder", "normalize_length"]  # same T, V; different weights would need different engines
+    g = Golden("normalize_length")
+    c = g.spec
+    dev = torch.device("cuda:0")
+    bs = build_search(g, dev)
+    from llm_guided_asr_b200 import synthetic as syn
+
+    xs = [torch.from_numpy(g["logp"]).to(dev)]
+    # ragged batch: shorter utterances made from other seeds
+    for seed, T in ((5, 50), (6, 72), (7, 33)):
+        xs.append(syn.random_logp(seed, T, c["V"]).to(dev))
+    batch = bs.decode_batch(xs, c["maxr"], c["minr"])
+    orc = oracle_from_golden(g)
+    for b, x in enumerate(xs):
+        alone = bs(x=x, maxlenratio=c["maxr"], minlenratio=c["minr"])
+        ref = orc.forward(x.cpu().numpy(), c["maxr"], c["minr"])
+        assert len(batch[b]) == len(alone) == len(ref)
+        for hb, ha, hr in zip(batch[b], alone, ref):
+            assert hb.yseq.tolist() == ha.yseq.tolist() == hr.yseq
+            assert float(hb.score) == float(ha.score)  # lock-step batching must not change a bit
+            assert abs(float(hb.score) - float(hr.score)) <= SCORE_ATOL
