@@ -350,8 +350,11 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
   int* r_flat = reinterpret_cast<int*>(r_total + W * R);  // [W*R]  h*V + tok  (tie order)
   int* sel = r_flat + W * R;                              // [W] record index per rank
   int* dest = sel + W;                                    // [W] >=0 running idx, -1-e ended idx e, INT_MIN dropped
-  __shared__ int sh_nsel, sh_nrun_new, sh_last;
+  __shared__ int sh_nsel;
   const int tid = threadIdx.x;
+  // read before any barrier: thread 0 updates these for the next step further down
+  const int cur_len = d.cur_len[b];
+  const int maxlen = d.maxlen[b], minlen = d.minlen[b];
 
   for (int e = tid; e < nrec; e += kSelThreads) {
     int h = e / n_rec_row, j = e - h * n_rec_row;
@@ -376,8 +379,6 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
   }
   __syncthreads();
 
-  const int cur_len = d.cur_len[b];
-  const int maxlen = d.maxlen[b], minlen = d.minlen[b];
   if (tid == 0) {
     const bool last = (step == maxlen - 1);
     int nsel = 0;
@@ -426,8 +427,6 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
     d.cur_len[b] = cur_len + 1;
     if (fin) d.done[b] = 1;
     sh_nsel = nsel;
-    sh_nrun_new = nrun_new;
-    sh_last = last ? 1 : 0;
   }
   __syncthreads();
   const int nsel = sh_nsel;
