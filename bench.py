@@ -1,0 +1,383 @@
+#!/usr/bin/env python3
+"""bench.py - decode throughput of the fused beam-search scoring path and its roofline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): LibriSpeech-conformer shape - a batch of 64 synthetic 15 s
+utterances (T = 374 encoder frames), V = 5000 BPE, beam 10, pre-beam 15, ctc_weight 0.3, one full
+scorer (the attention decoder's (B*beam, V) log-prob matrices, synthetic: log_softmax(2*randn), seed
+11+position), CTC posteriors log_softmax(3*randn) seed 7+utt, fixed 64 decode positions
+(maxlenratio = -64), fp32.  A bench "step" = one whole batch decode = CTCPrefixScoreTH.__init__ +
+init_hyp + 64 x (BatchBeamSearch.search + post_process).  The neural scorers that produce the
+matrices are out of the path.
+
+  value : utts/s with posteriors and matrices already resident in HBM
+  e2e   : utts/s through the C ABI from HOST (pinned) buffers, H2D of posteriors + every matrix and
+          D2H of the n-best inside the timed region
+  roofline : k_score_rows (the dominant kernel) algorithmic bytes / CUDA-event duration vs the
+          measured HBM copy bandwidth of MEASURED_PEAKS.json
+  cpu_baseline / --impl reference : the oracle port of the reference algorithm on the host cores.
+
+Multi-GPU: every rank decodes its own 64 utterances (weak scaling, no data-path collective), then a
+final gather of the best hypotheses to rank 0.
+"""
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG = dict(B=64, T=374, V=5000, beam=10, S=15, ctc_weight=0.3, L=64, K=1)
+AUDIO_SEC = 15.0
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def make_inputs(rank, cfg):
+    """CPU tensors: logp (B, T, V), tables (L, B*beam, V)."""
+    B, T, V, W, L = cfg["B"], cfg["T"], cfg["V"], cfg["beam"], cfg["L"]
+    logp = torch.empty(B, T, V)
+    for b in range(B):
+        g = torch.Generator().manual_seed(7 + 1000 * rank + b)
+        logp[b] = torch.log_softmax(3.0 * torch.randn(T, V, generator=g), dim=-1)
+    tables = torch.empty(L, B * W, V)
+    for i in range(L):
+        g = torch.Generator().manual_seed(11 + i + 100000 * rank)
+        tables[i] = torch.log_softmax(2.0 * torch.randn(B * W, V, generator=g), dim=-1)
+    return logp, tables
+
+
+def algorithmic_bytes(cfg, n_run_per_step):
+    """A_step = 4*[T_eff*(W*S + 1 + 4*W) + K*W*V] + 16*W per utterance and position."""
+    T, V, S, K = cfg["T"], cfg["V"], cfg["S"], cfg["K"]
+    total = 0
+    for l, ws in enumerate(n_run_per_step):
+        t_eff = T - max(l, 1)
+        for w in ws:
+            total += 4 * (t_eff * (w * S + 1 + 4 * w) + K * w * V) + 16 * w
+    return total
+
+
+class ClockSampler:
+    def __init__(self, index=0):
+        self.samples, self.reasons, self.stop = [], set(), False
+        self.index = index
+        self.th = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop:
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                    capture_output=True, text=True, timeout=5,
+                ).stdout.strip().split(",")
+                self.samples.append((float(out[0]), float(out[1])))
+                for n, v in zip(names, out[2:]):
+                    if v.strip().lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def __enter__(self):
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.th.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": sorted(self.reasons)}
+        return {
+            "sm_mhz": statistics.median(s[0] for s in self.samples),
+            "sm_max_mhz": max(s[1] for s in self.samples),
+            "reasons": sorted(self.reasons),
+            "samples": len(self.samples),
+        }
+
+
+# ---- the oracle port on the host cores (cpu_baseline / --impl reference) ---------------------------
+def _oracle_decode_one(args):
+    logp_b, tables_b, cfg = args  # (T, V), (L, beam, V)
+    from oracle.beam_search_oracle import BeamSearchOracle
+
+    V, W = cfg["V"], cfg["beam"]
+    eos = V - 1
+
+    def dec(ys):
+        return tables_b[ys.shape[1] - 1, : len(ys)]
+
+    orc = BeamSearchOracle(
+        dict(decoder=dec), dict(decoder=1.0 - cfg["ctc_weight"], ctc=cfg["ctc_weight"]), W, V, eos, eos, pre_beam_score_key="full"
+    )
+    nb = orc.forward(logp_b, -cfg["L"], 0.0)
+    return [(h.yseq, float(h.score)) for h in nb]
+
+
+def cpu_oracle_run(logp, tables, cfg, utts, procs):
+    """Decode `utts` utterance indices with the oracle, `procs` processes (job-level sharding as
+    egs2/*/asr.sh inference_nj).  Returns (seconds, results)."""
+    import multiprocessing as mp
+
+    W = cfg["beam"]
+    jobs = [(logp[b].numpy(), tables[:, b * W : (b + 1) * W].numpy(), cfg) for b in utts]
+    t0 = time.perf_counter()
+    if procs <= 1:
+        res = [_oracle_decode_one(j) for j in jobs]
+    else:
+        with mp.get_context("fork").Pool(procs) as pool:
+            res = pool.map(_oracle_decode_one, jobs)
+    return time.perf_counter() - t0, res
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    torch.set_num_threads(1)
+    cores = os.cpu_count() or 1
+    cfg = dict(CFG)
+    logp, tables = make_inputs(0, dict(cfg, B=min(cfg["B"], max(cores, 2))))
+    n_utts = min(logp.shape[0], cores)
+    times = []
+    for i in range(args.warmup + args.steps):
+        # bounded sample per step: one utterance per core, the same 64-position decode
+        dt, _ = cpu_oracle_run(logp, tables, cfg, list(range(n_utts)), cores)
+        if i >= args.warmup:
+            times.append(dt)
+    per_step = sum(times) / len(times)
+    value = n_utts / per_step
+    line = {
+        "impl": "reference",
+        "metric": "decode_utts_per_sec",
+        "value": value,
+        "unit": "utts/s",
+        "n_gpus": args.gpus,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": per_step * 1e3,
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "f32",
+        "data": "synthetic",
+        "config": bench_config(cfg),
+        "rtfx": value * AUDIO_SEC,
+        "cpu_baseline": {
+            "value": value, "unit": "utts/s", "cores": cores, "kind": "port",
+            "sample": f"{n_utts} utterances x {cfg['L']} positions per step, one process per core (numpy oracle port of CTCPrefixScoreTH + BatchBeamSearch)",
+        },
+        "e2e": {"value": value, "unit": "utts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def bench_config(cfg):
+    return {
+        "workload": "configs[1] LibriSpeech-conformer shape: 64 utts x 15 s (T=374), V=5000, beam=10, pre-beam=15, ctc_weight=0.3, 1 full scorer, 64 positions (maxlenratio=-64)",
+        "B_per_gpu": cfg["B"], "T": cfg["T"], "V": cfg["V"], "beam": cfg["beam"], "pre_beam": cfg["S"],
+        "positions": cfg["L"], "full_scorers": cfg["K"],
+        "l2": "inputs larger than L2: 481 MB posteriors + 819 MB matrices per step vs 126 MB L2",
+        "parallelism": "utterance sharding, one process per GPU, no data-path collective",
+    }
+
+
+def run_ours(args, rank, world, local_rank):
+    from llm_guided_asr_b200 import _lib
+    from llm_guided_asr_b200.engine import FusedStepEngine
+
+    dev = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(dev)
+    cfg = dict(CFG)
+    B, T, V, W, L = cfg["B"], cfg["T"], cfg["V"], cfg["beam"], cfg["L"]
+    eos = V - 1
+    logp, tables = make_inputs(rank, cfg)
+    d_logp = logp.to(dev)
+    d_tables = tables.to(dev)
+    h_logp = logp.pin_memory()
+    h_tables = tables.pin_memory()
+    eng = FusedStepEngine(B, T, V, W, cfg["S"], ["decoder"], "full", True, cfg["ctc_weight"], eos, eos, L, 1, False, device=dev)
+    consts, wts = [0.0], [1.0 - cfg["ctc_weight"]]
+    xl, mx, mn = [T] * B, [L] * B, [0] * B
+    mats_dev = [[d_tables[i]] for i in range(L)]
+    mats_host = [[h_tables[i]] for i in range(L)]
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize(dev)
+
+    def decode_resident():
+        eng.set_posteriors(d_logp, xl)
+        eng.begin(mx, mn, [eos])
+        eng.replay(mats_dev, consts, wts, ld=V)
+
+    def best_of(b):
+        toks, score, _ = eng.gather_ended(b)
+        j = int(np.argmax(score))  # first maximum = stable sort, best first
+        return toks[j], float(score[j])
+
+    def decode_host():
+        eng.replay_host(h_logp, xl, mx, mn, [eos], mats_host, consts, wts, ld=V)
+        return [best_of(b) for b in range(B)]
+
+    # ---- value: resident inputs -------------------------------------------------------------
+    for _ in range(args.warmup):
+        decode_resident()
+    barrier()
+    n0 = _lib.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clk:
+        ev0.record()
+        for _ in range(args.steps):
+            decode_resident()
+        ev1.record()
+        barrier()
+    launches = _lib.launch_count() - n0
+    ms_total = ev0.elapsed_time(ev1)
+    results_resident = [best_of(b) for b in range(B)]
+
+    # ---- roofline pass: per-kernel events, position by position ------------------------------
+    eng.set_posteriors(d_logp, xl)
+    eng.begin(mx, mn, [eos])
+    eng.set_profiling(True)
+    n_run_hist = []
+    nrun = np.ones(B, dtype=np.int64)
+    for i in range(L):
+        n_run_hist.append([int(v) for v in nrun])
+        eng.step(mats_dev[i], consts, wts)
+        nrun, done, _, _, act = eng.poll(with_parents=False)
+        nrun = np.where(np.asarray(done) != 0, 0, nrun)
+        if act == 0:
+            break
+    ms_rows, ms_sel, nsteps = eng.get_profile()
+    eng.set_profiling(False)
+    abytes = algorithmic_bytes(cfg, n_run_hist)
+    peak, peak_kind = peaks()
+    achieved = abytes / (ms_rows * 1e-3) / 1e9
+
+    # ---- e2e: host buffers ---------------------------------------------------------------------
+    for _ in range(max(1, min(args.warmup, 2))):
+        decode_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res_host = decode_host()
+        if world > 1:  # final hypothesis gather (tiny)
+            gathered = [None] * world if rank == 0 else None
+            torch.distributed.gather_object(res_host, gathered, dst=0)
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    assert res_host == results_resident, "host-buffer and resident decodes disagree"
+
+    t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms_total, e2e_ms = float(t[0]), float(t[1])
+    ms_step = ms_total / args.steps
+    value = world * B / (ms_step * 1e-3)
+    e2e_val = world * B / (e2e_ms / args.steps * 1e-3)
+    if rank != 0:
+        return
+
+    # ---- cpu baseline + parity on a bounded sample (rank 0) ------------------------------------
+    cpu = None
+    parity = None
+    if args.gpus == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        n_s = min(B, cores)
+        dt, ores = cpu_oracle_run(logp, tables, cfg, list(range(n_s)), cores)
+        cpu = {
+            "value": n_s / dt, "unit": "utts/s", "cores": cores, "kind": "port",
+            "sample": f"{n_s} of the {B} utterances x {L} positions, one process per core (numpy oracle port)",
+        }
+        tok_equal = all(results_resident[b][0] == ores[b][0][0] for b in range(n_s))
+        maxdiff = max(abs(results_resident[b][1] - ores[b][0][1]) for b in range(n_s))
+        parity = {"utts_checked": n_s, "tokens_equal": bool(tok_equal), "max_abs_score_diff": maxdiff}
+
+    line = {
+        "metric": "decode_utts_per_sec",
+        "value": value,
+        "unit": "utts/s",
+        "n_gpus": world,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": ms_step,
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "f32",
+        "data": "synthetic",
+        "config": bench_config(cfg),
+        "rtfx": value * AUDIO_SEC,
+        "us_per_position": ms_step * 1e3 / L,
+        "positions_run": len(n_run_hist),
+        "e2e": {
+            "value": e2e_val, "unit": "utts/s",
+            "h2d_bytes_per_step": int(logp.numel() * 4 + tables.numel() * 4 + 3 * B * 4 + 8),
+            "d2h_bytes_per_step": int(B * 4 * 6 + B * L * W * 8 + B * W * 40),
+            "ms_per_step": e2e_ms / args.steps,
+        },
+        "gpu_launches": int(launches),
+        "roofline": {
+            "bound": "hbm", "kernel": "k_score_rows", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "peak_kind": peak_kind, "traffic": None,
+            "algorithmic_bytes_per_launch": abytes / max(nsteps, 1),
+            "avg_launch_us": ms_rows * 1e3 / max(nsteps, 1),
+            "k_select_avg_launch_us": ms_sel * 1e3 / max(nsteps, 1),
+            "launches_timed": nsteps,
+        },
+        "cpu_baseline": cpu,
+        "parity": parity,
+        "clocks": clk.summary(),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        torch.distributed.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -122,6 +122,12 @@ int lgasr_poll(lgasr_handle* h, int32_t* h_n_running, int32_t* h_done, int32_t* 
 int lgasr_gather_ended(lgasr_handle* h, int utt, int32_t* n_ended, int32_t* max_len, int64_t* h_tokens,
                        int32_t* h_lens, float* h_score, float* h_scores, void* stream);
 
+/* Per-kernel device timing (bench.py "roofline"): when on, every step records CUDA events around
+ * its two kernels on the launching stream. lgasr_get_profile synchronises the events and returns
+ * the accumulated durations (ms) since profiling was switched on, and the number of steps. */
+int lgasr_set_profiling(lgasr_handle* h, int on);
+int lgasr_get_profile(lgasr_handle* h, float* ms_score_rows, float* ms_select, int32_t* n_steps);
+
 /* Whole-batch replay with pre-computed full-scorer matrices, device resident:
  * d_terms[step][k] -> (B*beam, V) matrices (flattened h_term_ptr[n_steps*K]); runs lgasr_begin's
  * state forward for up to n_steps positions without host round trips (bench.py "value" leg). */

@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -63,6 +64,9 @@ struct lgasr_handle {
   std::vector<float> c_score, c_scores;
   std::vector<int4> c_meta;
   std::vector<int> c_bp_par, c_bp_tok;
+  // per-kernel profiling
+  int profiling;
+  std::vector<cudaEvent_t> prof_ev;  // 3 per step
 };
 
 template <typename T>
@@ -193,17 +197,29 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
   h->xlens.assign(d.B, d.T);
   h->cache_valid = false;
 
-  // opt in to large dynamic shared memory
-  cudaError_t e = cudaSuccess;
-  switch (h->NL) {
-    case 1: e = cudaFuncSetAttribute(k_score_rows<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
-    case 2: e = cudaFuncSetAttribute(k_score_rows<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
-    default: e = cudaFuncSetAttribute(k_score_rows<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
-  }
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_sel);
-  if (e != cudaSuccess) {
-    lgasr_destroy(h);
-    return fail(LGASR_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  // opt in to large dynamic shared memory.  The attribute is per function and process wide, so it
+  // only ever grows (another handle may need more).
+  {
+    static std::mutex mu;
+    static size_t cur_rows[5] = {0, 0, 0, 0, 0}, cur_sel = 0;
+    std::lock_guard<std::mutex> lk(mu);
+    cudaError_t e = cudaSuccess;
+    if (h->smem_rows > cur_rows[h->NL]) {
+      switch (h->NL) {
+        case 1: e = cudaFuncSetAttribute(k_score_rows<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
+        case 2: e = cudaFuncSetAttribute(k_score_rows<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
+        default: e = cudaFuncSetAttribute(k_score_rows<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
+      }
+      if (e == cudaSuccess) cur_rows[h->NL] = h->smem_rows;
+    }
+    if (e == cudaSuccess && h->smem_sel > cur_sel) {
+      e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_sel);
+      if (e == cudaSuccess) cur_sel = h->smem_sel;
+    }
+    if (e != cudaSuccess) {
+      lgasr_destroy(h);
+      return fail(LGASR_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
   }
   *out = h;
   return LGASR_OK;
@@ -212,6 +228,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
 extern "C" int lgasr_destroy(lgasr_handle* h) {
   if (!h) return LGASR_OK;
   for (void* p : h->allocs) cudaFree(p);
+  for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->d_logp_stage) cudaFree(h->d_logp_stage);
   for (int s = 0; s < 2; ++s) {
@@ -318,14 +335,24 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st) {
   Dev& d = h->d;
   if (h->step >= d.maxlen_cap) return fail(LGASR_ESTATE, "step %d beyond max_len_cap %d", h->step, d.maxlen_cap);
   dim3 grid(d.W, d.B);
+  cudaEvent_t pe[3] = {nullptr, nullptr, nullptr};
+  if (h->profiling) {
+    for (int i = 0; i < 3; ++i) {
+      CK(cudaEventCreate(&pe[i]));
+      h->prof_ev.push_back(pe[i]);
+    }
+    CK(cudaEventRecord(pe[0], st));
+  }
   switch (h->NL) {
     case 1: k_score_rows<1><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
     case 2: k_score_rows<2><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
     default: k_score_rows<4><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
   }
   LAUNCH_CK();
+  if (h->profiling) CK(cudaEventRecord(pe[1], st));
   k_select<<<d.B, kSelThreads, h->smem_sel, st>>>(d, tm, h->pp, h->step);
   LAUNCH_CK();
+  if (h->profiling) CK(cudaEventRecord(pe[2], st));
   h->pp ^= 1;
   h->rp ^= 1;
   h->step += 1;
@@ -340,6 +367,32 @@ extern "C" int lgasr_step(lgasr_handle* h, const float* const* h_term_ptr, const
   Terms tm;
   TRY(fill_terms(h, tm, h_term_ptr, h_term_const, h_term_weight, ld));
   return step_impl(h, tm, (cudaStream_t)stream);
+}
+
+extern "C" int lgasr_set_profiling(lgasr_handle* h, int on) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
+  h->prof_ev.clear();
+  h->profiling = on ? 1 : 0;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_get_profile(lgasr_handle* h, float* ms_score_rows, float* ms_select, int32_t* n_steps) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  double a = 0.0, b = 0.0;
+  const size_t n = h->prof_ev.size() / 3;
+  for (size_t i = 0; i < n; ++i) {
+    float t0 = 0.f, t1 = 0.f;
+    CK(cudaEventSynchronize(h->prof_ev[3 * i + 2]));
+    CK(cudaEventElapsedTime(&t0, h->prof_ev[3 * i], h->prof_ev[3 * i + 1]));
+    CK(cudaEventElapsedTime(&t1, h->prof_ev[3 * i + 1], h->prof_ev[3 * i + 2]));
+    a += t0;
+    b += t1;
+  }
+  if (ms_score_rows) *ms_score_rows = (float)a;
+  if (ms_select) *ms_select = (float)b;
+  if (n_steps) *n_steps = (int)n;
+  return LGASR_OK;
 }
 
 extern "C" int lgasr_view(lgasr_handle* h, int which, void** d_ptr, int64_t* ld) {
@@ -554,8 +607,16 @@ extern "C" int lgasr_ctc_prefix_score(const float* d_xT, int T, int Tp, int V, i
   if (S > 0 && !d_ids) return fail(LGASR_EINVAL, "null ids");
   const size_t smem = (size_t)2 * Tp * sizeof(float);
   if (smem > 200 * 1024) return fail(LGASR_EINVAL, "T too large");
-  cudaError_t e = cudaFuncSetAttribute(k_ctc_prefix_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+  {
+    static std::mutex mu;
+    static size_t cur = 48 * 1024;
+    std::lock_guard<std::mutex> lk(mu);
+    if (smem > cur) {
+      cudaError_t e = cudaFuncSetAttribute(k_ctc_prefix_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+      cur = smem;
+    }
+  }
   k_ctc_prefix_score<<<n, 256, smem, (cudaStream_t)stream>>>(d_xT, T, Tp, V, blank, eos, d_r_prev, d_s_prev, d_last, olen,
                                                             reinterpret_cast<const long long*>(d_ids), S, d_scores, d_log_psi);
   LAUNCH_CK();
@@ -569,8 +630,16 @@ extern "C" int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blan
     return fail(LGASR_EINVAL, "bad argument");
   const size_t smem = (size_t)4 * Tp * sizeof(float);
   if (smem > 200 * 1024) return fail(LGASR_EINVAL, "T too large");
-  cudaError_t e = cudaFuncSetAttribute(k_ctc_select_state, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+  {
+    static std::mutex mu;
+    static size_t cur = 48 * 1024;
+    std::lock_guard<std::mutex> lk(mu);
+    if (smem > cur) {
+      cudaError_t e = cudaFuncSetAttribute(k_ctc_select_state, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+      cur = smem;
+    }
+  }
   k_ctc_select_state<<<m, 32, smem, (cudaStream_t)stream>>>(d_xT, T, Tp, blank, d_r_prev, d_last, d_sel_hyp, d_sel_tok, olen,
                                                            d_r_new);
   LAUNCH_CK();

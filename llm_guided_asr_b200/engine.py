@@ -179,6 +179,16 @@ class FusedStepEngine:
                 )
             )
 
+    def set_profiling(self, on: bool):
+        _lib.check(self.lib.lgasr_set_profiling(self._h, 1 if on else 0))
+
+    def get_profile(self):
+        """(ms in k_score_rows, ms in k_select, steps) accumulated since set_profiling(True)."""
+        a, b, n = C.c_float(), C.c_float(), C.c_int32()
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.lgasr_get_profile(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        return float(a.value), float(b.value), int(n.value)
+
     def poll(self, with_parents=True):
         """(n_running[B], done[B], parent[B][beam], token[B][beam], n_active) as numpy / int."""
         act = C.c_int32()
