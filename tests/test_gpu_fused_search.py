@@ -77,6 +77,13 @@ def test_decode_batch_equals_single_and_oracle():
         ref = orc.forward(x.cpu().numpy(), c["maxr"], c["minr"])
         assert len(batch[b]) == len(alone) == len(ref)
         for hb, ha, hr in zip(batch[b], alone, ref):
-            assert hb.yseq.tolist() == ha.yseq.tolist() == hr.yseq
-            assert float(hb.score) == float(ha.score)  # lock-step batching must not change a bit
+            assert hb.yseq.tolist() == ha.yseq.tolist()  # lock-step batching must not change a bit
+            assert float(hb.score) == float(ha.score)
+            if float(hr.score) < -1e9:
+                # CTC-impossible prefixes (more tokens than frames left): every one of the W*V entries
+                # is exactly -3e9 in fp32, torch.topk's pick among them is unspecified (the reference
+                # itself picks tokens 4,0,1 here, the oracle 0,1,2) = "documented exact-score tie".
+                assert float(hb.score) == float(hr.score) and len(hb.yseq) == len(hr.yseq)
+                continue
+            assert hb.yseq.tolist() == hr.yseq
             assert abs(float(hb.score) - float(hr.score)) <= SCORE_ATOL
