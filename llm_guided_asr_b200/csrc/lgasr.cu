@@ -5,6 +5,7 @@
 #include <climits>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -12,6 +13,7 @@
 
 #include "lgasr_kernels.cuh"
 #include "lgasr_scorer_kernels.cuh"
+#include "lgasr_step.cuh"
 
 using namespace lgasr;
 
@@ -45,6 +47,10 @@ struct lgasr_handle {
   int pp, rp, step, begun, have_post;
   int NL;
   size_t smem_rows, smem_sel;
+  StepLaunch sl;     // k_step launch geometry
+  size_t smem_step;
+  int ept;           // 8 or 16 elements per selection thread and chunk
+  int fused;         // 1: one k_step launch per position; 0: k_score_rows + k_select
   std::vector<void*> allocs;
   std::vector<long long> primer;
   std::vector<int> xlens;
@@ -146,6 +152,41 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     return fail(LGASR_EINVAL, "shared memory need too large (T=%d beam=%d)", d.T, d.W);
   }
 
+  // ---- k_step geometry -------------------------------------------------------------------------
+  {
+    const char* env = getenv("LGASR_LEGACY");
+    h->fused = (d.mode != kModeFullCtc) && !(env && env[0] == '1');
+    StepLaunch& sl = h->sl;
+    const int K = d.K > 0 ? d.K : 1;
+    h->ept = (d.V <= 1024 || K > 2) ? 8 : 16;
+    sl.CH = h->ept * kGroupThreads;
+    const int nchunks = (d.V + sl.CH - 1) / sl.CH;
+    int nst = 8192 / (K * sl.CH);
+    if (nst < 1) nst = 1;
+    if (nst > kMaxStages) nst = kMaxStages;
+    if (nst > nchunks) nst = nchunks;
+    sl.NST = nst;
+    sl.tma_rows = 0;  // decided per step from the pointers
+    long long arena = (long long)nst * K * sl.CH;
+    long long cand = (long long)n_sel * d.Tp;
+    if (cand > 8192) cand = 8192;
+    if (cand < d.Tp) cand = d.Tp;
+    if (d.mode == kModePreBeam && cand > arena) arena = cand;
+    const long long selw = (long long)d.W * d.R * 2 + 2 * d.W;
+    if (selw > arena) arena = selw;
+    arena = (arena + 3) & ~3LL;
+    sl.arena_floats = (int)arena;
+    int rpg = (int)(arena / d.Tp);
+    if (rpg < 1) rpg = 1;
+    if (rpg > n_sel) rpg = n_sel;
+    sl.rows_per_group = rpg;
+    h->smem_step = sizeof(StepSmem) + (size_t)6 * d.Tp * sizeof(float) + (size_t)arena * sizeof(float);
+    if (h->fused && h->smem_step > 220 * 1024) {
+      delete h;
+      return fail(LGASR_EINVAL, "shared memory need too large for the fused step (T=%d beam=%d K=%d)", d.T, d.W, d.K);
+    }
+  }
+
   const size_t BW = (size_t)d.B * d.W;
   int rc = 0;
   float* xT = nullptr;
@@ -165,9 +206,13 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     rc |= dalloc(h, &d.run_slot[p], BW);
   }
   int *maxlen = nullptr, *minlen = nullptr;
-  rc |= dalloc(h, &d.cur_len, d.B);
-  rc |= dalloc(h, &d.n_run, d.B);
-  rc |= dalloc(h, &d.done, d.B);
+  for (int p = 0; p < 2; ++p) {
+    rc |= dalloc(h, &d.cur_len[p], d.B);
+    rc |= dalloc(h, &d.n_run[p], d.B);
+    rc |= dalloc(h, &d.done[p], d.B);
+    rc |= dalloc(h, &d.rmeta[p], BW);
+  }
+  rc |= dalloc(h, &d.arrive, d.B);
   rc |= dalloc(h, &d.step_parent, BW);
   rc |= dalloc(h, &d.step_tok, BW);
   rc |= dalloc(h, &maxlen, d.B);
@@ -211,6 +256,14 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
         default: e = cudaFuncSetAttribute(k_score_rows<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_rows); break;
       }
       if (e == cudaSuccess) cur_rows[h->NL] = h->smem_rows;
+    }
+    static size_t cur_step[2] = {0, 0};
+    if (e == cudaSuccess && h->fused && h->smem_step > cur_step[h->ept == 16]) {
+      if (h->ept == 16)
+        e = cudaFuncSetAttribute(k_step<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      else
+        e = cudaFuncSetAttribute(k_step<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      if (e == cudaSuccess) cur_step[h->ept == 16] = h->smem_step;
     }
     if (e == cudaSuccess && h->smem_sel > cur_sel) {
       e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_sel);
@@ -325,6 +378,8 @@ static int fill_terms(lgasr_handle* h, Terms& tm, const float* const* ptr, const
     tm.ptr[k] = ptr ? ptr[k] : nullptr;
     tm.cst[k] = cst ? cst[k] : 0.f;
     tm.w[k] = w ? w[k] : 0.f;
+    tm.slot[k] = tm.nptr;
+    if (tm.ptr[k]) ++tm.nptr;
   }
   if (d.key >= 0 && !tm.ptr[d.key]) return fail(LGASR_EINVAL, "pre_beam_key term %d has no matrix", d.key);
   if (ld < d.V && d.K > 0) return fail(LGASR_EINVAL, "ld %lld < V %d", (long long)ld, d.V);
@@ -343,16 +398,34 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st) {
     }
     CK(cudaEventRecord(pe[0], st));
   }
-  switch (h->NL) {
-    case 1: k_score_rows<1><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
-    case 2: k_score_rows<2><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
-    default: k_score_rows<4><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
+  if (h->fused) {
+    StepLaunch sl = h->sl;
+    // TMA bulk copies need 16-byte aligned rows whose chunks are multiples of 16 bytes
+    bool al = (tm.nptr > 0) && (tm.ld % 4 == 0) && (d.V % 4 == 0);
+    for (int k = 0; k < tm.K; ++k)
+      if (tm.ptr[k]) al = al && ((reinterpret_cast<uintptr_t>(tm.ptr[k]) & 15) == 0);
+    sl.tma_rows = al ? 1 : 0;
+    if (h->ept == 16)
+      k_step<16><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
+    else
+      k_step<8><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
+    LAUNCH_CK();
+    if (h->profiling) {
+      CK(cudaEventRecord(pe[1], st));
+      CK(cudaEventRecord(pe[2], st));
+    }
+  } else {
+    switch (h->NL) {
+      case 1: k_score_rows<1><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
+      case 2: k_score_rows<2><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
+      default: k_score_rows<4><<<grid, kRowThreads, h->smem_rows, st>>>(d, tm, h->pp, h->rp); break;
+    }
+    LAUNCH_CK();
+    if (h->profiling) CK(cudaEventRecord(pe[1], st));
+    k_select<<<d.B, kSelThreads, h->smem_sel, st>>>(d, tm, h->pp, h->step);
+    LAUNCH_CK();
+    if (h->profiling) CK(cudaEventRecord(pe[2], st));
   }
-  LAUNCH_CK();
-  if (h->profiling) CK(cudaEventRecord(pe[1], st));
-  k_select<<<d.B, kSelThreads, h->smem_sel, st>>>(d, tm, h->pp, h->step);
-  LAUNCH_CK();
-  if (h->profiling) CK(cudaEventRecord(pe[2], st));
   h->pp ^= 1;
   h->rp ^= 1;
   h->step += 1;
@@ -401,12 +474,12 @@ extern "C" int lgasr_view(lgasr_handle* h, int which, void** d_ptr, int64_t* ld)
   int64_t l = 0;
   switch (which) {
     case 0: *d_ptr = d.yseq[h->pp]; l = d.Lcap; break;
-    case 1: *d_ptr = d.n_run; l = 1; break;
+    case 1: *d_ptr = d.n_run[h->pp]; l = 1; break;
     case 2: *d_ptr = d.step_parent; l = d.W; break;
     case 3: *d_ptr = d.step_tok; l = d.W; break;
-    case 4: *d_ptr = d.done; l = 1; break;
+    case 4: *d_ptr = d.done[h->pp]; l = 1; break;
     case 5: *d_ptr = d.score[h->pp]; l = d.W; break;
-    case 6: *d_ptr = d.cur_len; l = 1; break;
+    case 6: *d_ptr = d.cur_len[h->pp]; l = 1; break;
     default: return fail(LGASR_EINVAL, "unknown view %d", which);
   }
   if (ld) *ld = l;
@@ -420,8 +493,8 @@ extern "C" int lgasr_poll(lgasr_handle* h, int32_t* h_n_running, int32_t* h_done
   Dev& d = h->d;
   const int BW = d.B * d.W;
   int* pin = h->h_pin;
-  CK(cudaMemcpyAsync(pin, d.n_run, sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(pin + d.B, d.done, sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(pin, d.n_run[h->pp], sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(pin + d.B, d.done[h->pp], sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
   if (h_parent) CK(cudaMemcpyAsync(pin + 2 * d.B, d.step_parent, sizeof(int) * BW, cudaMemcpyDeviceToHost, st));
   if (h_token) CK(cudaMemcpyAsync(pin + 2 * d.B + BW, d.step_tok, sizeof(int) * BW, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));

@@ -23,6 +23,8 @@ struct Terms {
   const float* ptr[kMaxTerms];
   float cst[kMaxTerms];
   float w[kMaxTerms];
+  int slot[kMaxTerms];  // index of term k among the terms that have a matrix (staging order)
+  int nptr;             // number of terms with a matrix
   int K;
   long long ld;
 };
@@ -39,9 +41,11 @@ struct Dev {
   float* scores[2];      // [B][W][NS]
   long long* yseq[2];    // [B][W][Lcap]
   int* run_slot[2];      // [B][W] slot of a running hyp in the best list of the step that made it
-  int* cur_len;          // [B]
-  int* n_run;            // [B]
-  int* done;             // [B]
+  int* cur_len[2];       // [B]  ping-pong like every per-step state: a step reads [pp], writes [pp^1]
+  int* n_run[2];         // [B]
+  int* done[2];          // [B]
+  int4* rmeta[2];        // [B][W] (parent slot or -1, last token, parent's last token or -1, 0)
+  int* arrive;           // [B] CTAs of the utterance that finished scoring in the current launch
   int* step_parent;      // [B][W]
   int* step_tok;         // [B][W]
   const int* maxlen;     // [B]
@@ -166,7 +170,7 @@ __device__ __forceinline__ void warp_ctc_state(const float* __restrict__ xT_b,  
 template <int NL>
 __global__ void __launch_bounds__(kRowThreads) k_score_rows(Dev d, Terms tm, int pp, int rp) {
   const int b = blockIdx.y, h = blockIdx.x;
-  if (d.done[b] || h >= d.n_run[b]) return;
+  if (d.done[pp][b] || h >= d.n_run[pp][b]) return;
   extern __shared__ float smem[];
   const int Tp = d.Tp;
   float* bA = smem;  // r_sum
@@ -183,7 +187,7 @@ __global__ void __launch_bounds__(kRowThreads) k_score_rows(Dev d, Terms tm, int
   const int T = d.xlen[b];
   const int row = b * d.W + h;
   const long long rowoff = (long long)row * tm.ld;
-  const int cur_len = d.cur_len[b];
+  const int cur_len = d.cur_len[pp][b];
   const int olen = cur_len - 1;
   const long long* yrow = d.yseq[pp] + (long long)row * d.Lcap;
   const int last = (int)yrow[cur_len - 1];
@@ -196,7 +200,7 @@ __global__ void __launch_bounds__(kRowThreads) k_score_rows(Dev d, Terms tm, int
 
   const int first_stream_warp = d.use_ctc ? 1 : 0;
   if (d.use_ctc && warp == 0) {
-    const int par = d.step_parent[row];
+    const int par = d.rmeta[pp][row].x;
     const int has_parent = par >= 0;
     const float* r_par = d.r[rp] + ((long long)(b * d.W + (has_parent ? par : h)) * 2) * Tp;
     float* r_out = d.r[rp ^ 1] + ((long long)row * 2) * Tp;
@@ -337,12 +341,13 @@ __global__ void __launch_bounds__(kRowThreads) k_score_rows(Dev d, Terms tm, int
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp, int step) {
-  const int b = blockIdx.x;
-  if (d.done[b]) return;
-  const int n_run = d.n_run[b];
-  if (n_run <= 0) return;
-  extern __shared__ float smem[];
+// Selection of one utterance (all kSelThreads threads of a CTA): global top-beam over the candidate
+// records of its running hypotheses (batch_beam, batch_beam_search.py:101-128), hypothesis
+// bookkeeping (:325-363), post_process (:365-429) and end_detect (e2e_asr_common.py:17-48).
+// Reads state [pp], writes state [pp^1].  smem: >= W*R*8 + W*8 bytes.
+__device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b, int pp, int step, float* smem) {
+  const int tid = threadIdx.x;
+  const int n_run = d.n_run[pp][b];
   const int R = d.R, W = d.W;
   const int n_rec_row = (d.mode == kModePreBeam) ? d.S + 1 : d.W;
   const int nrec = n_run * n_rec_row;
@@ -351,43 +356,104 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
   int* sel = r_flat + W * R;                              // [W] record index per rank
   int* dest = sel + W;                                    // [W] >=0 running idx, -1-e ended idx e, INT_MIN dropped
   __shared__ int sh_nsel;
-  const int tid = threadIdx.x;
-  // read before any barrier: thread 0 updates these for the next step further down
-  const int cur_len = d.cur_len[b];
+  __shared__ float sh_redv[kSelThreads / 32];
+  __shared__ int sh_redf[kSelThreads / 32], sh_rede[kSelThreads / 32];
+  const int cur_len = d.cur_len[pp][b];
   const int maxlen = d.maxlen[b], minlen = d.minlen[b];
+  // scalars of the serial part, fetched early (only this utterance's selection ever writes them)
+  int n_end0 = 0;
+  float best_all0 = 0.f;
+  if (tid == 0) {
+    n_end0 = d.n_ended[b];
+    best_all0 = d.best_all[b];
+  }
 
   for (int e = tid; e < nrec; e += kSelThreads) {
     int h = e / n_rec_row, j = e - h * n_rec_row;
     long long o = (long long)(b * W + h) * R + j;
-    int tok = d.cand_tok[o];
-    r_total[e] = d.cand_total[o];
+    int tok = __ldcg(d.cand_tok + o);  // written by other CTAs of this launch: read through L2
+    r_total[e] = __ldcg(d.cand_total + o);
     r_flat[e] = tok >= 0 ? h * d.V + tok : -1;
   }
   if (tid < W) sel[tid] = -1;
   __syncthreads();
-  // rank by counting
-  for (int e = tid; e < nrec; e += kSelThreads) {
-    int fe = r_flat[e];
-    if (fe < 0) continue;
-    float ve = r_total[e];
-    int rank = 0;
-    for (int o = 0; o < nrec; ++o) {
-      int fo = r_flat[o];
-      if (fo >= 0 && better(r_total[o], fo, ve, fe)) ++rank;
+  if (nrec <= 2 * kSelThreads) {
+    // rank by counting
+    for (int e = tid; e < nrec; e += kSelThreads) {
+      int fe = r_flat[e];
+      if (fe < 0) continue;
+      float ve = r_total[e];
+      int rank = 0;
+      for (int o = 0; o < nrec; ++o) {
+        int fo = r_flat[o];
+        if (fo >= 0 && better(r_total[o], fo, ve, fe)) ++rank;
+      }
+      if (rank < W) sel[rank] = e;
     }
-    if (rank < W) sel[rank] = e;
+    __syncthreads();
+  } else {
+    // wide beams: W rounds of block arg-best (each round takes the best record after the previous pick)
+    float pv = INFINITY;
+    int pf = -1;
+    for (int r = 0; r < W; ++r) {
+      float bv = -INFINITY;
+      int bf = 0x7fffffff, be = -1;
+      for (int e = tid; e < nrec; e += kSelThreads) {
+        int fe = r_flat[e];
+        if (fe < 0) continue;
+        float ve = r_total[e];
+        if (!better(pv, pf, ve, fe)) continue;  // not after the previous pick
+        if (be < 0 || better(ve, fe, bv, bf)) {
+          bv = ve;
+          bf = fe;
+          be = e;
+        }
+      }
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) {
+        float ov = __shfl_xor_sync(FULLMASK, bv, o);
+        int of = __shfl_xor_sync(FULLMASK, bf, o);
+        int oe = __shfl_xor_sync(FULLMASK, be, o);
+        if (oe >= 0 && (be < 0 || better(ov, of, bv, bf))) {
+          bv = ov;
+          bf = of;
+          be = oe;
+        }
+      }
+      if ((tid & 31) == 0) {
+        sh_redv[tid >> 5] = bv;
+        sh_redf[tid >> 5] = bf;
+        sh_rede[tid >> 5] = be;
+      }
+      __syncthreads();
+      bv = sh_redv[0];
+      bf = sh_redf[0];
+      be = sh_rede[0];
+      for (int w = 1; w < kSelThreads / 32; ++w) {
+        if (sh_rede[w] >= 0 && (be < 0 || better(sh_redv[w], sh_redf[w], bv, bf))) {
+          bv = sh_redv[w];
+          bf = sh_redf[w];
+          be = sh_rede[w];
+        }
+      }
+      if (tid == 0) sel[r] = be;
+      __syncthreads();
+      if (be < 0) break;
+      pv = bv;
+      pf = bf;
+    }
   }
-  __syncthreads();
 
   if (tid == 0) {
     const bool last = (step == maxlen - 1);
     int nsel = 0;
     while (nsel < W && sel[nsel] >= 0) ++nsel;
     int nrun_new = 0;
-    int n_end = d.n_ended[b];
-    float best_all = d.best_all[b];
+    int n_end = n_end0;
+    float best_all = best_all0;
     float* bbl = d.best_by_len + (long long)b * (d.Lcap + 2);
     const int new_len = cur_len + 1 + (last ? 1 : 0);
+    float best_new = -INFINITY;  // best ended score of this step: all of them have length new_len
     for (int j = 0; j < nsel; ++j) {
       int e = sel[j];
       int tok = r_flat[e] % d.V;
@@ -398,8 +464,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
           float sc = r_total[e];
           d.end_score[(long long)b * d.Ecap + n_end] = sc;
           d.end_meta[(long long)b * d.Ecap + n_end] = make_int4(step, j, new_len, last ? 1 : 0);
-          if (sc > best_all) best_all = sc;
-          if (sc > bbl[new_len]) bbl[new_len] = sc;
+          if (sc > best_new) best_new = sc;
           ++n_end;
         } else {
           dest[j] = INT_MIN;
@@ -408,11 +473,15 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
         dest[j] = nrun_new++;
       }
     }
-    d.n_ended[b] = n_end;
-    d.best_all[b] = best_all;
+    if (best_new > -INFINITY) {
+      if (best_new > best_all) best_all = best_new;
+      if (best_new > bbl[new_len]) bbl[new_len] = best_new;
+      d.n_ended[b] = n_end;
+      d.best_all[b] = best_all;
+    }
     // end detection (e2e_asr_common.py:17-48): lengths step, step-1, step-2
     bool fin = (nrun_new == 0) || last;
-    if (d.end_detect && n_end > 0) {
+    if (!fin && d.end_detect && n_end > 0) {
       int count = 0;
       for (int m = 0; m < 3; ++m) {
         int len = step - m;
@@ -423,9 +492,9 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
       }
       if (count == 3) fin = true;
     }
-    d.n_run[b] = nrun_new;
-    d.cur_len[b] = cur_len + 1;
-    if (fin) d.done[b] = 1;
+    d.n_run[pp ^ 1][b] = nrun_new;
+    d.cur_len[pp ^ 1][b] = cur_len + 1;
+    d.done[pp ^ 1][b] = fin ? 1 : 0;
     sh_nsel = nsel;
   }
   __syncthreads();
@@ -438,9 +507,9 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
     const int h = e / n_rec_row, jj = e - h * n_rec_row;
     const int prow = b * W + h;
     const long long o = (long long)prow * R + jj;
-    const int tok = d.cand_tok[o];
+    const int tok = r_flat[e] - h * d.V;
     const float total = r_total[e];
-    const float psi = d.cand_psi[o];
+    const float psi = __ldcg(d.cand_psi + o);
     // trellis
     const long long bpo = ((long long)b * d.maxlen_cap + step) * W + j;
     d.bp_par[bpo] = d.run_slot[pp][prow];
@@ -452,6 +521,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
       d.score[pp ^ 1][nrow] = total;
       d.s_prev[pp ^ 1][nrow] = psi;
       d.run_slot[pp ^ 1][nrow] = j;
+      d.rmeta[pp ^ 1][nrow] = make_int4(h, tok, d.rmeta[pp][prow].y, 0);
       d.step_parent[nrow] = h;
       d.step_tok[nrow] = tok;
       sc_out = d.scores[pp ^ 1] + (long long)nrow * NS;
@@ -478,8 +548,26 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
     const long long* src = d.yseq[pp] + (long long)(b * W + h) * d.Lcap;
     long long* dst = d.yseq[pp ^ 1] + (long long)(b * W + dj) * d.Lcap;
     for (int t = lane; t < cur_len; t += 32) dst[t] = src[t];
-    if (lane == 0) dst[cur_len] = (long long)(r_flat[e] % d.V);
+    if (lane == 0) dst[cur_len] = (long long)(r_flat[e] - h * d.V);
   }
+}
+
+// a finished utterance carries its flags over to the next state buffer
+__device__ __forceinline__ void utt_carry_done(const Dev& d, int b, int pp) {
+  d.n_run[pp ^ 1][b] = 0;
+  d.cur_len[pp ^ 1][b] = d.cur_len[pp][b];
+  d.done[pp ^ 1][b] = 1;
+}
+
+// stand-alone selection launch (used after k_score_rows, i.e. for the full-vocabulary CTC mode)
+__global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp, int step) {
+  const int b = blockIdx.x;
+  extern __shared__ float smem[];
+  if (d.done[pp][b] || d.n_run[pp][b] <= 0) {
+    if (threadIdx.x == 0) utt_carry_done(d, b, pp);
+    return;
+  }
+  utt_select(d, tm, b, pp, step, smem);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -536,9 +624,12 @@ __global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_
   const int tid = threadIdx.x;
   const int W = d.W;
   if (tid == 0) {
-    d.cur_len[b] = primer_len;
-    d.n_run[b] = 1;
-    d.done[b] = (d.maxlen[b] <= 0) ? 1 : 0;
+    for (int p = 0; p < 2; ++p) {
+      d.cur_len[p][b] = primer_len;
+      d.n_run[p][b] = 1;
+      d.done[p][b] = (d.maxlen[b] <= 0) ? 1 : 0;
+    }
+    d.arrive[b] = 0;
     d.n_ended[b] = 0;
     d.best_all[b] = -INFINITY;
   }
@@ -552,6 +643,9 @@ __global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_
     }
     d.step_parent[b * W + i] = -1;
     d.step_tok[b * W + i] = -1;
+    const int last = (int)primer[primer_len - 1];
+    d.rmeta[0][b * W + i] = make_int4(-1, last, -1, 0);
+    d.rmeta[1][b * W + i] = make_int4(-1, last, -1, 0);
   }
   for (int i = tid; i < primer_len; i += blockDim.x) {
     d.yseq[0][(long long)(b * W) * d.Lcap + i] = primer[i];
