@@ -128,6 +128,11 @@ int lgasr_gather_ended(lgasr_handle* h, int utt, int32_t* n_ended, int32_t* max_
 int lgasr_set_profiling(lgasr_handle* h, int on);
 int lgasr_get_profile(lgasr_handle* h, float* ms_score_rows, float* ms_select, int32_t* n_steps);
 
+/* Debug time line of the fused step kernel: when the environment variable LGASR_TRACE is set at
+ * lgasr_create, every CTA of k_step stamps clock64() at its phase boundaries; this copies the
+ * [B][beam][2 groups][16] stamps of the most recent step to h_out (n = capacity in elements). */
+int lgasr_debug_trace(lgasr_handle* h, int64_t* h_out, int64_t n);
+
 /* Whole-batch replay with pre-computed full-scorer matrices, device resident:
  * d_terms[step][k] -> (B*beam, V) matrices (flattened h_term_ptr[n_steps*K]); runs lgasr_begin's
  * state forward for up to n_steps positions without host round trips (bench.py "value" leg). */

@@ -57,6 +57,7 @@ PROTOTYPES = {
     "lgasr_gather_ended": (_I, [_P, _I, _PI32, _PI32, _PI64, _PI32, _PF, _PF, _P]),
     "lgasr_set_profiling": (_I, [_P, _I]),
     "lgasr_get_profile": (_I, [_P, _PF, _PF, _PI32]),
+    "lgasr_debug_trace": (_I, [_P, _PI64, _I64]),
     "lgasr_decode_replay": (_I, [_P, _I, C.POINTER(_P), _PF, _PF, _I64, _P]),
     "lgasr_decode_replay_host": (_I, [_P, _P, _PI32, _PI32, _PI32, _PI64, _I, C.POINTER(_P), _PF, _PF, _I64, _P]),
     "lgasr_transpose_posteriors": (_I, [_P, _I, _I, _I, _I, _P, _I, _P]),

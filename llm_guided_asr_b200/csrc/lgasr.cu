@@ -213,6 +213,10 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     rc |= dalloc(h, &d.rmeta[p], BW);
   }
   rc |= dalloc(h, &d.arrive, d.B);
+  if (getenv("LGASR_TRACE")) {
+    rc |= dalloc(h, &d.trace, BW * 32);
+    if (!rc) cudaMemset(d.trace, 0, BW * 32 * sizeof(long long));
+  }
   rc |= dalloc(h, &d.step_parent, BW);
   rc |= dalloc(h, &d.step_tok, BW);
   rc |= dalloc(h, &maxlen, d.B);
@@ -465,6 +469,15 @@ extern "C" int lgasr_get_profile(lgasr_handle* h, float* ms_score_rows, float* m
   if (ms_score_rows) *ms_score_rows = (float)a;
   if (ms_select) *ms_select = (float)b;
   if (n_steps) *n_steps = (int)n;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_debug_trace(lgasr_handle* h, int64_t* h_out, int64_t n) {
+  if (!h || !h_out) return fail(LGASR_EINVAL, "null argument");
+  if (!h->d.trace) return fail(LGASR_ESTATE, "tracing is off (set LGASR_TRACE=1 before lgasr_create)");
+  const int64_t have = (int64_t)h->d.B * h->d.W * 32;
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(h_out, h->d.trace, sizeof(long long) * (size_t)(n < have ? n : have), cudaMemcpyDeviceToHost));
   return LGASR_OK;
 }
 

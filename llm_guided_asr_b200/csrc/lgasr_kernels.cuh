@@ -61,6 +61,7 @@ struct Dev {
   float* end_scores;     // [B][Ecap][NS]
   float* best_by_len;    // [B][Lcap + 2]
   float* best_all;       // [B]
+  long long* trace;      // debug: [B][W][2][16] clock64 stamps of k_step phases (NULL = off)
 };
 
 // modes
@@ -71,12 +72,10 @@ constexpr int kModeFullCtc = 2;  // CTC over the whole vocabulary (ctc_weight ==
 // sum_k w_k * s_k[v] in the reference's fp32 order: ((0 + w0*s0) + w1*s1) + ...  (no FMA contraction)
 __device__ __forceinline__ float fuse_at(const Terms& t, long long rowoff, int v) {
   float acc = 0.f;
-#pragma unroll
-  for (int k = 0; k < kMaxTerms; ++k) {
-    if (k < t.K) {
-      float s = t.ptr[k] ? __ldg(t.ptr[k] + rowoff + v) : t.cst[k];
-      acc = __fadd_rn(acc, __fmul_rn(t.w[k], s));
-    }
+#pragma unroll 1
+  for (int k = 0; k < t.K; ++k) {
+    float s = t.ptr[k] ? __ldg(t.ptr[k] + rowoff + v) : t.cst[k];
+    acc = __fadd_rn(acc, __fmul_rn(t.w[k], s));
   }
   return acc;
 }

@@ -213,6 +213,13 @@ struct __align__(16) StepSmem {
   int pend_idx[kPendCap];
 };
 
+// debug time line: stamp i of group grp (0 ctc / all, 1 sel) of this CTA
+#define LGASR_TR(grp, i)                                                                      \
+  do {                                                                                         \
+    if (d.trace && (tid & (kGroupThreads - 1)) == 0 && (tid >> 7) == (grp))                    \
+      d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2 + (grp)) * 16 + (i)] = clock64(); \
+  } while (0)
+
 constexpr int kBarCtc = 1, kBarSel = 2;  // named barriers of the two groups (0 = __syncthreads)
 
 // issue the TMA copies of chunk c of this hypothesis' full-scorer rows into its stage
@@ -223,9 +230,9 @@ __device__ __forceinline__ void issue_row_chunk(const Terms& tm, long long rowof
   const uint32_t bytes = (uint32_t)n * 4u;
   unsigned long long* bar = &S->bar_full[stage];
   mbar_expect_tx(reinterpret_cast<uint64_t*>(bar), bytes * (uint32_t)tm.nptr);
-#pragma unroll
-  for (int k = 0; k < kMaxTerms; ++k)
-    if (k < tm.K && tm.ptr[k])
+#pragma unroll 1
+  for (int k = 0; k < tm.K; ++k)
+    if (tm.ptr[k])
       bulk_g2s(arena + ((long long)stage * tm.nptr + tm.slot[k]) * CH, tm.ptr[k] + rowoff + (long long)c * CH, bytes,
                reinterpret_cast<uint64_t*>(bar));
 }
@@ -284,6 +291,8 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
     mbar_fence_init();
   }
   __syncthreads();
+  LGASR_TR(0, 0);
+  LGASR_TR(1, 0);
 
   if (tid < kGroupThreads) {
     // ======================= ctc group: CTC state of this hypothesis ==================================
@@ -301,8 +310,10 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
         }
       }
       mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
+      LGASR_TR(0, 1);
       float* r_out = d.r[rp ^ 1] + ((long long)row * 2) * Tp;
       group_ctc_state(bR0, bR1, bA, bB, bC, bD, r_out, has_parent, last == rm.z, olen - 1, T, Tp, g, S->ws, kBarCtc);
+      LGASR_TR(0, 2);
     }
   } else if (mode != kModeFullCtc) {
     // ======================= sel group: fused row stream + exact top-n_sel ============================
@@ -321,45 +332,65 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
       const int e0 = c * CH;
       float val[EPT];
       // ---- values of this thread: elements e0 + 4*(j + 128*i) + u ---------------------------------
+      const int n_ch = min(CH, V - e0);
+      const float* sb;
       if (tma) {
         mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[stage]), (uint32_t)((c / NST) & 1));
-        const float* sb = arena + (long long)stage * tm.nptr * CH;
+        sb = arena + (long long)stage * tm.nptr * CH;
+        if (c == 0) LGASR_TR(1, 1);
+      } else {
+        // rows that are not 16-byte aligned: the group stages the chunk with plain loads
+        sb = arena;
+#pragma unroll 1
+        for (int k = 0; k < tm.K; ++k) {
+          const float* src = tm.ptr[k];
+          if (!src) continue;
+          src += rowoff + e0;
+          float* dst = arena + tm.slot[k] * CH;
+          for (int i = j; i < n_ch; i += kGroupThreads) dst[i] = __ldg(src + i);
+        }
+        group_bar(kBarSel);
+      }
+      {
+        float4 acc[EPT / 4];
+        if (d.key >= 0) {
+          const float* base = sb + tm.slot[d.key] * CH;
 #pragma unroll
-        for (int i = 0; i < EPT / 4; ++i) {
-          const int q = j + kGroupThreads * i;
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (e0 + 4 * q < V) {
-            if (d.key >= 0) {
-              acc = *reinterpret_cast<const float4*>(sb + tm.slot[d.key] * CH + 4 * q);
+          for (int i = 0; i < EPT / 4; ++i) acc[i] = *reinterpret_cast<const float4*>(base + 4 * (j + kGroupThreads * i));
+        } else {
+#pragma unroll
+          for (int i = 0; i < EPT / 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+          for (int k = 0; k < tm.K; ++k) {
+            const float wk = tm.w[k];
+            if (tm.ptr[k]) {
+              const float* base = sb + tm.slot[k] * CH;
+#pragma unroll
+              for (int i = 0; i < EPT / 4; ++i) {
+                const float4 sv = *reinterpret_cast<const float4*>(base + 4 * (j + kGroupThreads * i));
+                acc[i].x = __fadd_rn(acc[i].x, __fmul_rn(wk, sv.x));
+                acc[i].y = __fadd_rn(acc[i].y, __fmul_rn(wk, sv.y));
+                acc[i].z = __fadd_rn(acc[i].z, __fmul_rn(wk, sv.z));
+                acc[i].w = __fadd_rn(acc[i].w, __fmul_rn(wk, sv.w));
+              }
             } else {
+              const float cv = __fmul_rn(wk, tm.cst[k]);
 #pragma unroll
-              for (int k = 0; k < kMaxTerms; ++k) {
-                if (k < tm.K) {
-                  float4 s;
-                  if (tm.ptr[k])
-                    s = *reinterpret_cast<const float4*>(sb + tm.slot[k] * CH + 4 * q);
-                  else
-                    s = make_float4(tm.cst[k], tm.cst[k], tm.cst[k], tm.cst[k]);
-                  acc.x = __fadd_rn(acc.x, __fmul_rn(tm.w[k], s.x));
-                  acc.y = __fadd_rn(acc.y, __fmul_rn(tm.w[k], s.y));
-                  acc.z = __fadd_rn(acc.z, __fmul_rn(tm.w[k], s.z));
-                  acc.w = __fadd_rn(acc.w, __fmul_rn(tm.w[k], s.w));
-                }
+              for (int i = 0; i < EPT / 4; ++i) {
+                acc[i].x = __fadd_rn(acc[i].x, cv);
+                acc[i].y = __fadd_rn(acc[i].y, cv);
+                acc[i].z = __fadd_rn(acc[i].z, cv);
+                acc[i].w = __fadd_rn(acc[i].w, cv);
               }
             }
           }
-          val[4 * i + 0] = acc.x;
-          val[4 * i + 1] = acc.y;
-          val[4 * i + 2] = acc.z;
-          val[4 * i + 3] = acc.w;
         }
-      } else {
 #pragma unroll
-        for (int i = 0; i < EPT; ++i) {
-          const int e = e0 + 4 * (j + kGroupThreads * (i >> 2)) + (i & 3);
-          float f = 0.f;
-          if (e < V) f = (d.key < 0) ? fuse_at(tm, rowoff, e) : __ldg(tm.ptr[d.key] + rowoff + e);
-          val[i] = f;
+        for (int i = 0; i < EPT / 4; ++i) {
+          val[4 * i + 0] = acc[i].x;
+          val[4 * i + 1] = acc[i].y;
+          val[4 * i + 2] = acc[i].z;
+          val[4 * i + 3] = acc[i].w;
         }
       }
       // the fused score of eos is needed even when eos is not a pre-beam candidate (:180-181)
@@ -465,6 +496,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
         if (!ovf) break;
       }
     }
+    LGASR_TR(1, 2);
     // ---- gather the candidates' posterior rows (first group) by TMA ------------------------------------
     if (mode == kModePreBeam && j == 0) {
       const int cl = S->cur_list;
@@ -486,6 +518,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
     }
   }
   __syncthreads();
+  LGASR_TR(0, 3);
 
   // ======================= all warps: candidate records ===============================================
   const int cl = S->cur_list;
@@ -538,6 +571,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
         }
       }
       mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand), (uint32_t)(grp & 1));
+      LGASR_TR(0, 4);
       for (int jr = g0 + warp; jr < g1; jr += kWarps) {
         const int c = ti[jr];
         const float wfull = (d.key < 0) ? tv[jr] : fuse_at(tm, rowoff, c);
@@ -594,6 +628,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
   }
 
   // ======================= ticket: the last CTA of the utterance runs the selection ==================
+  LGASR_TR(0, 5);
   __threadfence();
   __syncthreads();
   if (tid == 0) {
@@ -601,10 +636,12 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
     S->last_flag = (old == n_run - 1) ? 1 : 0;
   }
   __syncthreads();
+  LGASR_TR(0, 6);
   if (!S->last_flag) return;
   if (tid == 0) d.arrive[b] = 0;
   __threadfence();
   utt_select(d, tm, b, pp, step, arena);
+  LGASR_TR(0, 7);
 }
 
 }  // namespace lgasr

@@ -1,0 +1,40 @@
+#!/usr/bin/env python3
+"""Phase time line of k_step on the bench workload (LGASR_TRACE=1): cycles since CTA start, median over CTAs."""
+import os, sys
+os.environ["LGASR_TRACE"] = "1"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import ctypes as C
+import numpy as np, torch
+import bench
+from llm_guided_asr_b200 import _lib
+from llm_guided_asr_b200.engine import FusedStepEngine
+
+cfg = dict(bench.CFG)
+if len(sys.argv) > 1:
+    cfg["B"] = int(sys.argv[1])
+B, T, V, W, L = cfg["B"], cfg["T"], cfg["V"], cfg["beam"], 12
+dev = torch.device("cuda:0")
+logp, tables = bench.make_inputs(0, dict(cfg, L=L))
+d_logp, d_tables = logp.to(dev), tables.to(dev)
+eos = V - 1
+eng = FusedStepEngine(B, T, V, W, cfg["S"], ["decoder"], "full", True, cfg["ctc_weight"], eos, eos, L, 1, False, device=dev)
+eng.set_posteriors(d_logp, [T] * B)
+eng.begin([L] * B, [0] * B, [eos])
+for i in range(L):
+    eng.step([d_tables[i]], [0.0], [1.0 - cfg["ctc_weight"]])
+out = np.zeros(B * W * 32, np.int64)
+_lib.check(eng.lib.lgasr_debug_trace(eng._h, out.ctypes.data_as(_lib._PI64), out.size))
+tr = out.reshape(B * W, 2, 16)
+t0 = tr[:, 0, 0:1]
+names0 = ["start", "ctc_in", "ctc_done", "joined", "cand_in", "records", "ticket", "select_done"]
+names1 = ["start", "row0_in", "sel_done"]
+rel0 = (tr[:, 0, :8] - t0).astype(np.float64)
+rel1 = (tr[:, 1, :3] - t0).astype(np.float64)
+for i, n in enumerate(names0):
+    v = rel0[:, i][tr[:, 0, i] != 0]
+    if len(v):
+        print(f"ctc/all {n:12s} n={len(v):4d} median={np.median(v):9.0f} p90={np.percentile(v, 90):9.0f} max={v.max():9.0f} cycles")
+for i, n in enumerate(names1):
+    v = rel1[:, i][tr[:, 1, i] != 0]
+    if len(v):
+        print(f"sel     {n:12s} n={len(v):4d} median={np.median(v):9.0f} p90={np.percentile(v, 90):9.0f} max={v.max():9.0f} cycles")
