@@ -146,7 +146,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
   if (h->NL == 3) h->NL = 4;
   const int capS = 32 * h->NL;
   h->smem_rows = (size_t)4 * d.Tp * sizeof(float) + (size_t)kRowWarps * capS * 8 + (size_t)capS * 8;
-  h->smem_sel = (size_t)d.W * d.R * 8 + (size_t)d.W * 8;
+  h->smem_sel = (size_t)d.W * d.R * 12 + (size_t)d.W * 8;
   if (h->smem_rows > 220 * 1024 || h->smem_sel > 220 * 1024) {
     delete h;
     return fail(LGASR_EINVAL, "shared memory need too large (T=%d beam=%d)", d.T, d.W);
@@ -158,10 +158,11 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     h->fused = (d.mode != kModeFullCtc) && !(env && env[0] == '1');
     StepLaunch& sl = h->sl;
     const int K = d.K > 0 ? d.K : 1;
-    h->ept = (d.V <= 1024 || K > 2) ? 8 : 16;
-    sl.CH = h->ept * kGroupThreads;
+    // elements per selection thread and chunk: 16 when one scorer matrix is streamed and the row is long
+    h->ept = (K == 1 && d.V > 8 * kSelGroup) ? 16 : 8;
+    sl.CH = h->ept * kSelGroup;
     const int nchunks = (d.V + sl.CH - 1) / sl.CH;
-    int nst = 8192 / (K * sl.CH);
+    int nst = 6144 / (K * sl.CH);
     if (nst < 1) nst = 1;
     if (nst > kMaxStages) nst = kMaxStages;
     if (nst > nchunks) nst = nchunks;
@@ -169,10 +170,10 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     sl.tma_rows = 0;  // decided per step from the pointers
     long long arena = (long long)nst * K * sl.CH;
     long long cand = (long long)n_sel * d.Tp;
-    if (cand > 8192) cand = 8192;
+    if (cand > 6144) cand = 6144;
     if (cand < d.Tp) cand = d.Tp;
     if (d.mode == kModePreBeam && cand > arena) arena = cand;
-    const long long selw = (long long)d.W * d.R * 2 + 2 * d.W;
+    const long long selw = (long long)d.W * d.R * 3 + 2 * d.W;
     if (selw > arena) arena = selw;
     arena = (arena + 3) & ~3LL;
     sl.arena_floats = (int)arena;

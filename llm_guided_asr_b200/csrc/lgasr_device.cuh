@@ -18,12 +18,13 @@
 namespace lgasr {
 
 // m + log(exp(a-m) + exp(b-m)), the two-operand torch.logsumexp (one of the exps is exp(0) = 1)
-// MUFU.EX2 / MUFU.LG2 (2^-22 relative): the argument of the log is in [1, 2], so the absolute error of the
-// result is ~1e-7, far below the fp32 rounding of the O(1e2..1e3) operands themselves.
+// Accurate expf/logf on purpose: r values reach magnitudes of 1e2..1e3 where one fp32 ulp is already ~6e-5,
+// so the 1e-4 score bar only holds if the dominant terms are evaluated like the reference evaluates them
+// (MUFU-approximate exp/log measured 9e-5 off on the bench workload; this form measured 0.0).
 __device__ __forceinline__ float lse2(float a, float b) {
   float m = fmaxf(a, b);
   float d = fminf(a, b) - m;  // <= 0
-  return m + __logf(1.0f + __expf(d));
+  return m + logf(1.0f + expf(d));
 }
 
 // total order used by every selection: larger value first, then smaller index

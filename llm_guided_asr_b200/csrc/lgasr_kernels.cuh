@@ -340,23 +340,30 @@ __global__ void __launch_bounds__(kRowThreads) k_score_rows(Dev d, Terms tm, int
 }
 
 // ------------------------------------------------------------------------------------------
+// total score back from a packed record key
+__device__ __forceinline__ float key_total(unsigned long long k) {
+  const unsigned u = (unsigned)(k >> 32);
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
 // Selection of one utterance (all kSelThreads threads of a CTA): global top-beam over the candidate
 // records of its running hypotheses (batch_beam, batch_beam_search.py:101-128), hypothesis
 // bookkeeping (:325-363), post_process (:365-429) and end_detect (e2e_asr_common.py:17-48).
-// Reads state [pp], writes state [pp^1].  smem: >= W*R*8 + W*8 bytes.
+// Reads state [pp], writes state [pp^1].  smem: >= W*R*12 + W*8 bytes (16-byte aligned).
 __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b, int pp, int step, float* smem) {
   const int tid = threadIdx.x;
   const int n_run = d.n_run[pp][b];
   const int R = d.R, W = d.W;
   const int n_rec_row = (d.mode == kModePreBeam) ? d.S + 1 : d.W;
   const int nrec = n_run * n_rec_row;
-  float* r_total = smem;                                  // [W*R]
-  int* r_flat = reinterpret_cast<int*>(r_total + W * R);  // [W*R]  h*V + tok  (tie order)
-  int* sel = r_flat + W * R;                              // [W] record index per rank
-  int* dest = sel + W;                                    // [W] >=0 running idx, -1-e ended idx e, INT_MIN dropped
+  // packed records: key = (ordered total << 32) | ~(h*V + tok): larger key = higher total, then lower flat index
+  unsigned long long* r_key = reinterpret_cast<unsigned long long*>(smem);  // [W*R]   0 = invalid
+  float* r_psi = reinterpret_cast<float*>(r_key + W * R);                   // [W*R]
+  int* sel = reinterpret_cast<int*>(r_psi + W * R);                         // [W] record index per rank
+  int* dest = sel + W;  // [W] >=0 running idx, -1-e ended idx e, INT_MIN dropped
   __shared__ int sh_nsel;
-  __shared__ float sh_redv[kSelThreads / 32];
-  __shared__ int sh_redf[kSelThreads / 32], sh_rede[kSelThreads / 32];
+  __shared__ unsigned long long sh_redk[kSelThreads / 32];
+  __shared__ int sh_rede[kSelThreads / 32];
   const int cur_len = d.cur_len[pp][b];
   const int maxlen = d.maxlen[b], minlen = d.minlen[b];
   // scalars of the serial part, fetched early (only this utterance's selection ever writes them)
@@ -368,78 +375,67 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
   }
 
   for (int e = tid; e < nrec; e += kSelThreads) {
-    int h = e / n_rec_row, j = e - h * n_rec_row;
-    long long o = (long long)(b * W + h) * R + j;
-    int tok = __ldcg(d.cand_tok + o);  // written by other CTAs of this launch: read through L2
-    r_total[e] = __ldcg(d.cand_total + o);
-    r_flat[e] = tok >= 0 ? h * d.V + tok : -1;
+    const int h = e / n_rec_row, j = e - h * n_rec_row;
+    const long long o = (long long)(b * W + h) * R + j;
+    const int tok = __ldcg(d.cand_tok + o);  // written by other CTAs of this launch: read through L2
+    const float tot = __ldcg(d.cand_total + o);
+    r_psi[e] = __ldcg(d.cand_psi + o);
+    unsigned u = __float_as_uint(tot + 0.0f);
+    u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    r_key[e] = tok >= 0 ? (((unsigned long long)u << 32) | (unsigned)(~(h * d.V + tok))) : 0ull;
   }
   if (tid < W) sel[tid] = -1;
   __syncthreads();
   if (nrec <= 2 * kSelThreads) {
     // rank by counting
     for (int e = tid; e < nrec; e += kSelThreads) {
-      int fe = r_flat[e];
-      if (fe < 0) continue;
-      float ve = r_total[e];
+      const unsigned long long ke = r_key[e];
+      if (ke == 0ull) continue;
       int rank = 0;
-      for (int o = 0; o < nrec; ++o) {
-        int fo = r_flat[o];
-        if (fo >= 0 && better(r_total[o], fo, ve, fe)) ++rank;
-      }
+#pragma unroll 4
+      for (int o = 0; o < nrec; ++o) rank += (r_key[o] > ke) ? 1 : 0;
       if (rank < W) sel[rank] = e;
     }
     __syncthreads();
   } else {
-    // wide beams: W rounds of block arg-best (each round takes the best record after the previous pick)
-    float pv = INFINITY;
-    int pf = -1;
+    // wide beams: W rounds of block arg-best (each round takes the best record below the previous pick)
+    unsigned long long pk = ~0ull;
     for (int r = 0; r < W; ++r) {
-      float bv = -INFINITY;
-      int bf = 0x7fffffff, be = -1;
+      unsigned long long bk = 0ull;
+      int be = -1;
       for (int e = tid; e < nrec; e += kSelThreads) {
-        int fe = r_flat[e];
-        if (fe < 0) continue;
-        float ve = r_total[e];
-        if (!better(pv, pf, ve, fe)) continue;  // not after the previous pick
-        if (be < 0 || better(ve, fe, bv, bf)) {
-          bv = ve;
-          bf = fe;
+        const unsigned long long ke = r_key[e];
+        if (ke != 0ull && ke < pk && ke > bk) {
+          bk = ke;
           be = e;
         }
       }
 #pragma unroll
       for (int o = 16; o >= 1; o >>= 1) {
-        float ov = __shfl_xor_sync(FULLMASK, bv, o);
-        int of = __shfl_xor_sync(FULLMASK, bf, o);
-        int oe = __shfl_xor_sync(FULLMASK, be, o);
-        if (oe >= 0 && (be < 0 || better(ov, of, bv, bf))) {
-          bv = ov;
-          bf = of;
+        const unsigned long long ok = __shfl_xor_sync(FULLMASK, bk, o);
+        const int oe = __shfl_xor_sync(FULLMASK, be, o);
+        if (ok > bk) {
+          bk = ok;
           be = oe;
         }
       }
       if ((tid & 31) == 0) {
-        sh_redv[tid >> 5] = bv;
-        sh_redf[tid >> 5] = bf;
+        sh_redk[tid >> 5] = bk;
         sh_rede[tid >> 5] = be;
       }
       __syncthreads();
-      bv = sh_redv[0];
-      bf = sh_redf[0];
+      bk = sh_redk[0];
       be = sh_rede[0];
       for (int w = 1; w < kSelThreads / 32; ++w) {
-        if (sh_rede[w] >= 0 && (be < 0 || better(sh_redv[w], sh_redf[w], bv, bf))) {
-          bv = sh_redv[w];
-          bf = sh_redf[w];
+        if (sh_redk[w] > bk) {
+          bk = sh_redk[w];
           be = sh_rede[w];
         }
       }
       if (tid == 0) sel[r] = be;
       __syncthreads();
       if (be < 0) break;
-      pv = bv;
-      pf = bf;
+      pk = bk;
     }
   }
 
@@ -455,12 +451,12 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
     float best_new = -INFINITY;  // best ended score of this step: all of them have length new_len
     for (int j = 0; j < nsel; ++j) {
       int e = sel[j];
-      int tok = r_flat[e] % d.V;
+      int tok = (int)(~(unsigned)r_key[e]) % d.V;
       bool is_eos = last || tok == d.eos;
       if (is_eos) {
         if (step >= minlen && n_end < d.Ecap) {
           dest[j] = -1 - n_end;
-          float sc = r_total[e];
+          float sc = key_total(r_key[e]);
           d.end_score[(long long)b * d.Ecap + n_end] = sc;
           d.end_meta[(long long)b * d.Ecap + n_end] = make_int4(step, j, new_len, last ? 1 : 0);
           if (sc > best_new) best_new = sc;
@@ -503,12 +499,11 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
   if (tid < nsel) {
     const int j = tid;
     const int e = sel[j];
-    const int h = e / n_rec_row, jj = e - h * n_rec_row;
+    const int h = e / n_rec_row;
     const int prow = b * W + h;
-    const long long o = (long long)prow * R + jj;
-    const int tok = r_flat[e] - h * d.V;
-    const float total = r_total[e];
-    const float psi = __ldcg(d.cand_psi + o);
+    const int tok = (int)(~(unsigned)r_key[e]) - h * d.V;
+    const float total = key_total(r_key[e]);
+    const float psi = r_psi[e];
     // trellis
     const long long bpo = ((long long)b * d.maxlen_cap + step) * W + j;
     d.bp_par[bpo] = d.run_slot[pp][prow];
@@ -547,7 +542,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
     const long long* src = d.yseq[pp] + (long long)(b * W + h) * d.Lcap;
     long long* dst = d.yseq[pp ^ 1] + (long long)(b * W + dj) * d.Lcap;
     for (int t = lane; t < cur_len; t += 32) dst[t] = src[t];
-    if (lane == 0) dst[cur_len] = (long long)(r_flat[e] - h * d.V);
+    if (lane == 0) dst[cur_len] = (long long)((int)(~(unsigned)r_key[e]) - h * d.V);
   }
 }
 

@@ -2,16 +2,16 @@
 //
 //   grid (beam, B), 256 threads: one CTA per running hypothesis, warp-specialised.
 //
-//   warps 0-3  "ctc"   : CTC state of the hypothesis = forward recursion of its parent's state by its
+//   warps 0-1  "ctc"   : CTC state of the hypothesis = forward recursion of its parent's state by its
 //                         last token (what CTCPrefixScoreTH.__call__ computes for EVERY candidate,
 //                         ctc_prefix_score.py:122-160, and select_state then picks, scorers/ctc.py:56-62),
-//                         done only for the survivor, as a 128-thread log-semiring affine scan over the
+//                         done only for the survivor, as a 64-thread log-semiring affine scan over the
 //                         frames.  Inputs (parent r, the token's and the blank's posterior rows) arrive by
 //                         1-D TMA bulk copies (cp.async.bulk + mbarrier).
-//   warps 4-7  "sel"   : stream the K full-scorer rows (TMA bulk copies, up to 4 stages in flight), fuse
+//   warps 2-7  "sel"   : stream the K full-scorer rows (TMA bulk copies, up to 4 stages in flight), fuse
 //                         sum_k w_k*s_k in the reference's fp32 order and keep the exact pre-beam top-S
-//                         (threshold + rank-by-counting; no (n,V) temporaries, no topk launch;
-//                         batch_beam_search.py:279-308).
+//                         (threshold from lane maxima, ballot compaction, rank-by-counting on packed
+//                         64-bit keys; no (n,V) temporaries, no topk launch; batch_beam_search.py:279-308).
 //   all warps          : the S candidates' posterior rows xT[b][c][:] are gathered by TMA into shared
 //                         memory; log psi = logsumexp_t(phi[t-1] + x[t,c]) (+) r^n_{start-1} per warp
 //                         (ctc_prefix_score.py:163-185), then w_ctc*(psi - s_prev) + fused + running score
@@ -23,14 +23,15 @@
 namespace lgasr {
 
 constexpr int kStepThreads = 256;
-constexpr int kGroupThreads = 128;  // threads of the ctc group and of the sel group
-constexpr int kGroupWarps = 4;
+constexpr int kCtcWarps = 2, kCtcThreads = 32 * kCtcWarps;    // warps 0-1
+constexpr int kSelWarps = 6, kSelGroup = 32 * kSelWarps;       // warps 2-7
 constexpr int kMaxStages = 4;
 constexpr int kPendCap = 256;
 constexpr int kTopCap = 128;  // == LGASR_MAX_PREBEAM
+constexpr int kStepWarps = kStepThreads / 32;
 
 struct StepLaunch {
-  int CH;              // floats per chunk per term (1024 or 2048)
+  int CH;              // floats per chunk per term (EPT * kSelGroup)
   int NST;             // stages in flight
   int tma_rows;        // 1: full-scorer rows are 16-byte aligned -> bulk copies; 0: plain loads
   int arena_floats;    // union buffer: row stages | candidate rows | selection scratch
@@ -69,7 +70,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
-__device__ __forceinline__ void group_bar(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(kGroupThreads) : "memory"); }
+__device__ __forceinline__ void group_bar(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 
 // monotone map float -> uint32 (for redux.sync max)
 __device__ __forceinline__ unsigned f2ord(float f) {
@@ -80,16 +83,27 @@ __device__ __forceinline__ float ord2f(unsigned u) {
   return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
-// ---- 128-thread affine scan -------------------------------------------------------------------------
-// y[t] = lse2(y[t-1] + a[t], b[t]) for t in [start, T), y[start-1] = y0 (the recursion of
-// ctc_prefix_score.py:155-160).  a, y: shared memory; y holds b[t] on entry, y[t] on exit.
-// g: thread index in the group; ws: 2*kGroupWarps floats of shared scratch.  Ends with a group barrier.
-__device__ __forceinline__ void group_affine_scan(const float* a, float* y, int start, int T, float y0, int g, float* ws,
-                                                  int bar_id) {
+// (value, index) packed into one sortable key: larger key = better = larger value, then smaller index
+// (the total order of every selection, identical to lgasr::better).  +0.0f canonicalises -0.
+__device__ __forceinline__ unsigned long long pack_key(float v, int idx) {
+  return ((unsigned long long)f2ord(v + 0.0f) << 32) | (unsigned)(~idx);
+}
+__device__ __forceinline__ float key_val(unsigned long long k) { return ord2f((unsigned)(k >> 32)); }
+__device__ __forceinline__ int key_idx(unsigned long long k) { return (int)(~(unsigned)k); }
+
+
+// ---- group affine scan ------------------------------------------------------------------------------
+// y[t] = lse2(y[t-1] + a[t], b(t)) for t in [start, T), y[start-1] = y0 (the recursion of
+// ctc_prefix_score.py:155-160) by the kCtcThreads threads of the ctc group.  a, y: shared memory;
+// b(t): functor evaluated once per frame by the thread that owns the frame.
+// g: thread index in the group; ws: 2*kCtcWarps floats of shared scratch.  Ends with a group barrier.
+template <typename BF>
+__device__ __forceinline__ void group_affine_scan(const float* a, float* y, BF bfun, int start, int T, float y0, int g,
+                                                  float* ws, int bar_id) {
   const int n = T - start;
   if (n <= 0) return;  // group-uniform
   const int lane = g & 31, w = g >> 5;
-  int L = (n + kGroupThreads - 1) / kGroupThreads;
+  int L = (n + kCtcThreads - 1) / kCtcThreads;
   L |= 1;  // odd segment length: the lanes of a warp hit distinct banks
   int s0 = start + g * L;
   int s1 = s0 + L;
@@ -99,11 +113,11 @@ __device__ __forceinline__ void group_affine_scan(const float* a, float* y, int 
   float cur = LGASR_NEG, A = 0.f;
   for (int t = s0; t < s1; ++t) {
     const float at = a[t];
-    cur = lse2(cur + at, y[t]);
+    cur = lse2(cur + at, bfun(t));
     y[t] = cur;
     A += at;
   }
-  // inclusive scan of the segment summaries (A, B) inside the warp: (A1,B1) then (A2,B2) = (A1+A2, lse2(B1+A2, B2))
+  // inclusive scan of the segment summaries inside the warp: (A1,B1) then (A2,B2) = (A1+A2, lse2(B1+A2, B2))
   float SA = A, SB = cur;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -116,7 +130,7 @@ __device__ __forceinline__ void group_affine_scan(const float* a, float* y, int 
   }
   if (lane == 31) {
     ws[w] = SA;
-    ws[kGroupWarps + w] = SB;
+    ws[kCtcWarps + w] = SB;
   }
   float ea = __shfl_up_sync(FULLMASK, SA, 1);
   float eb = __shfl_up_sync(FULLMASK, SB, 1);
@@ -124,11 +138,11 @@ __device__ __forceinline__ void group_affine_scan(const float* a, float* y, int 
     ea = 0.f;
     eb = LGASR_NEG;
   }
-  group_bar(bar_id);
+  group_bar(bar_id, kCtcThreads);
   // summaries of the preceding warps, then this thread's exclusive prefix inside the warp
   float PA = 0.f, PB = LGASR_NEG;
   for (int i = 0; i < w; ++i) {
-    const float wa = ws[i], wb = ws[kGroupWarps + i];
+    const float wa = ws[i], wb = ws[kCtcWarps + i];
     PB = lse2(PB + wa, wb);
     PA += wa;
   }
@@ -141,57 +155,80 @@ __device__ __forceinline__ void group_affine_scan(const float* a, float* y, int 
     run += a[t];
     y[t] = lse2(yin + run, y[t]);
   }
-  group_bar(bar_id);
+  group_bar(bar_id, kCtcThreads);
 }
 
-// CTC state of hypothesis (b, h) by the 128 threads of the ctc group.
-// smem rows (Tp floats each): bR0/bR1 = parent r^n / r^b (TMA), bA = x[:, tok] (TMA), bC = x[:, blank] (TMA),
-// bB, bD scratch.  On exit: bA[t] = r_sum[t] = lse2(r^n, r^b), bD[t] = r^b[t] for t in [0, T); r_out written.
-__device__ __forceinline__ void group_ctc_state(const float* bR0, const float* bR1, float* bA, float* bB, float* bC,
-                                                float* bD, float* __restrict__ r_out, int has_parent, int same,
-                                                int olen_par, int T, int Tp, int g, float* ws, int bar_id) {
-  if (!has_parent) {
-    for (int t = g; t < T; t += kGroupThreads) {
-      const float rn = bR0[t], rb = bR1[t];
+// CTC state of hypothesis (b, h) by the ctc group.
+//
+// State format of the fused path (handle-internal): row 0 = r^n, row 1 = r_sum = lse2(r^n, r^b).  r^b is
+// not stored: r^b[t] = r_sum[t-1] + x_blank[t] for t >= start (exactly how :155-160 produces it), log-zero
+// before; for the initial hypothesis r^n is log-zero and r^b == r_sum (:82-93).  That makes the second
+// recursion produce r_sum directly (s_t = lse2(s_{t-1} + x_blank[t], r^n_t)) and saves two log-add-exp per frame.
+//
+// smem rows (Tp floats each): bR0/bR1 = parent r^n / r_sum (TMA), bA = x[:, tok] (TMA), bC = x[:, blank]
+// (TMA), bB, bD scratch.  r_out (global) receives the state.  On exit, for u in [0, Tp):
+//   bR0[u] = r_sum[u-1]   and   bR1[u] = r^b[u-1]   for pstart <= u < T, LGASR_NEG elsewhere
+// (pstart = max(olen, 1) of THIS hypothesis): the phi arrays of the psi phase, shifted by one frame so that
+// phi[t-1] + x[t] is an aligned element-wise sum.  *psi_eos = r_sum[T-1].
+__device__ __forceinline__ void group_ctc_state(float* bR0, float* bR1, const float* bA, float* bB, const float* bC,
+                                                float* bD, float* __restrict__ r_out, int has_parent, int par_initial,
+                                                int same, int olen_par, int T, int Tp, int g, float* ws, float* psi_eos,
+                                                int bar_id) {
+  const int start = olen_par > 1 ? olen_par : 1;           // first frame of the recursion that makes this state
+  const int pstart = olen_par + 1 > 1 ? olen_par + 1 : 1;  // max(olen, 1) of this hypothesis
+  float rn0 = LGASR_LOGZERO;
+  if (has_parent) {
+    const int start_par = olen_par - 1 > 1 ? olen_par - 1 : 1;  // the parent's own recursion start
+    rn0 = (olen_par == 0) ? bA[0] : LGASR_LOGZERO;               // r[start-1, 0]  (:128-129)
+    // r^n: a = x_tok, b[t] = phi_parent[t-1] + x_tok[t]; phi = r_sum, or r^b for a repeated token (:131-140)
+    group_affine_scan(
+        bA, bB,
+        [&](int t) {
+          const int u = t - 1;
+          float phi = bR1[u];
+          if (same && !par_initial) phi = (u >= start_par) ? bR1[u - 1] + bC[u] : LGASR_LOGZERO;
+          return phi + bA[t];
+        },
+        start, T, rn0, g, ws, bar_id);
+    // r_sum: a = x_blank, b[t] = r^n[t]   (s_t = lse2(r^b_t, r^n_t), r^b_t = s_{t-1} + x_blank[t])
+    group_affine_scan(
+        bC, bD, [&](int t) { return bB[t]; }, start, T, rn0, g, ws, bar_id);
+  }
+  for (int u = g; u <= Tp; u += kCtcThreads) {
+    const int t = u - 1;  // state of frame t
+    float rn = LGASR_LOGZERO, rs = LGASR_LOGZERO, rb = LGASR_LOGZERO;
+    if (t >= 0 && t < T) {
+      if (!has_parent) {
+        rn = bR0[t];
+        rs = bR1[t];
+        rb = rs;
+      } else if (t >= start) {
+        rn = bB[t];
+        rs = bD[t];
+        rb = ((t - 1 >= start) ? bD[t - 1] : rn0) + bC[t];
+      } else if (t == start - 1) {
+        rn = rn0;
+        rs = rn0;
+      }
       r_out[t] = rn;
-      r_out[Tp + t] = rb;
-      bA[t] = lse2(rn, rb);
-      bD[t] = rb;
+      r_out[Tp + t] = rs;
     }
-    return;
-  }
-  const int start = olen_par > 1 ? olen_par : 1;
-  for (int t = g; t < T; t += kGroupThreads) {
-    const float rn = bR0[t], rb = bR1[t];
-    bD[t] = same ? rb : lse2(rn, rb);  // phi of the parent (ctc_prefix_score.py:131-140)
-  }
-  group_bar(bar_id);
-  const float rn0 = (olen_par == 0) ? bA[0] : LGASR_LOGZERO;  // r[start-1, 0]  (:128-129)
-  for (int t = start + g; t < T; t += kGroupThreads) bB[t] = bD[t - 1] + bA[t];
-  group_bar(bar_id);
-  group_affine_scan(bA, bB, start, T, rn0, g, ws, bar_id);  // bB = r^n
-  for (int t = start + g; t < T; t += kGroupThreads) {
-    const float prev = (t - 1 >= start) ? bB[t - 1] : rn0;
-    bD[t] = prev + bC[t];
-  }
-  group_bar(bar_id);
-  group_affine_scan(bC, bD, start, T, LGASR_LOGZERO, g, ws, bar_id);  // bD = r^b
-  for (int t = g; t < T; t += kGroupThreads) {
-    float rn, rb;
-    if (t >= start) {
-      rn = bB[t];
-      rb = bD[t];
-    } else if (t == start - 1) {
-      rn = rn0;
-      rb = LGASR_LOGZERO;
-    } else {
-      rn = LGASR_LOGZERO;
-      rb = LGASR_LOGZERO;
+    if (t == T - 1) *psi_eos = rs;
+    if (u < Tp) {
+      const bool in = (u >= pstart && u < T);
+      // !has_parent: bR0/bR1[t] are still read by the thread that owns u = t + 1: stage in bB/bD
+      float* o0 = has_parent ? bR0 : bB;
+      float* o1 = has_parent ? bR1 : bD;
+      o0[u] = in ? rs : LGASR_NEG;
+      o1[u] = in ? rb : LGASR_NEG;
     }
-    r_out[t] = rn;
-    r_out[Tp + t] = rb;
-    bA[t] = lse2(rn, rb);
-    bD[t] = rb;
+  }
+  if (!has_parent) {
+    group_bar(bar_id, kCtcThreads);
+    for (int u = g; u < Tp; u += kCtcThreads) {
+      bR0[u] = bB[u];
+      bR1[u] = bD[u];
+    }
   }
 }
 
@@ -199,24 +236,20 @@ __device__ __forceinline__ void group_ctc_state(const float* bR0, const float* b
 struct __align__(16) StepSmem {
   unsigned long long bar_full[kMaxStages];  // full-scorer row stages
   unsigned long long bar_ctc;               // parent state + token row + blank row
-  unsigned long long bar_cand;              // candidate rows
+  unsigned long long bar_cand[kStepWarps];  // candidate rows, one barrier per consuming warp
+  unsigned long long keys[2][kTopCap + kPendCap];  // [cur]: sorted top list (n_top) followed by the pending pushes
   int pend_cnt, overflow, n_top, cur_list;
-  float tau_v;
-  int tau_i;
-  float w_eos;
-  int last_flag;
-  float ws[2 * kGroupWarps];
-  unsigned wkth[kGroupWarps];
-  float top_val[2][kTopCap];
-  int top_idx[2][kTopCap];
-  float pend_val[kPendCap];
-  int pend_idx[kPendCap];
+  unsigned long long tau;  // push threshold (key of the n_sel-th best so far; 0 = none)
+  float w_eos, psi_eos;
+  int last_flag, pad0;
+  float ws[2 * kCtcWarps];
+  unsigned wkth[kSelWarps];
 };
 
 // debug time line: stamp i of group grp (0 ctc / all, 1 sel) of this CTA
-#define LGASR_TR(grp, i)                                                                      \
-  do {                                                                                         \
-    if (d.trace && (tid & (kGroupThreads - 1)) == 0 && (tid >> 7) == (grp))                    \
+#define LGASR_TR(grp, i)                                                                       \
+  do {                                                                                          \
+    if (d.trace && tid == ((grp) ? kCtcThreads : 0))                                            \
       d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2 + (grp)) * 16 + (i)] = clock64(); \
   } while (0)
 
@@ -237,8 +270,31 @@ __device__ __forceinline__ void issue_row_chunk(const Terms& tm, long long rowof
                reinterpret_cast<uint64_t*>(bar));
 }
 
+// gather the posterior rows of candidates [g0, g1) of the sorted top list into the arena: lane w < 8 serves
+// the barrier of consuming warp w (candidates g0+w, g0+w+8, ...).  Called by one full warp.
+__device__ __forceinline__ void issue_cand_rows(const Dev& d, const unsigned long long* keys, int g0, int g1,
+                                                const float* xT_b, float* arena, StepSmem* S, int lane) {
+  const int Tp = d.Tp;
+  const uint32_t rb = (uint32_t)Tp * 4u;
+  fence_proxy_async();
+  if (lane < kStepWarps) {
+    uint32_t bytes = 0;
+    for (int i = g0 + lane; i < g1; i += kStepWarps) {
+      const int cc = key_idx(keys[i]);
+      if (cc != d.eos && !(d.eos != d.blank && cc == d.blank)) bytes += rb;
+    }
+    uint64_t* bar = reinterpret_cast<uint64_t*>(&S->bar_cand[lane]);
+    mbar_expect_tx(bar, bytes);
+    for (int i = g0 + lane; i < g1; i += kStepWarps) {
+      const int cc = key_idx(keys[i]);
+      if (cc != d.eos && !(d.eos != d.blank && cc == d.blank))
+        bulk_g2s(arena + (long long)(i - g0) * Tp, xT_b + (long long)cc * Tp, rb, bar);
+    }
+  }
+}
+
 template <int EPT>
-__global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaunch sl, int pp, int rp, int step) {
+__global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepLaunch sl, int pp, int rp, int step) {
   const int b = blockIdx.y, h = blockIdx.x;
   const int tid = threadIdx.x;
   {
@@ -258,7 +314,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
   float* bC = bB + Tp;
   float* bD = bC + Tp;
   float* arena = bD + Tp;
-  constexpr int CH = EPT * kGroupThreads;
+  constexpr int CH = EPT * kSelGroup;
   const int NST = sl.NST;
 
   const int lane = tid & 31, warp = tid >> 5;
@@ -280,21 +336,22 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
 #pragma unroll
     for (int i = 0; i < kMaxStages; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_full[i]), 1);
     mbar_init(reinterpret_cast<uint64_t*>(&S->bar_ctc), 1);
-    mbar_init(reinterpret_cast<uint64_t*>(&S->bar_cand), 1);
+#pragma unroll
+    for (int i = 0; i < kStepWarps; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_cand[i]), 1);
     S->pend_cnt = 0;
     S->overflow = 0;
     S->n_top = 0;
     S->cur_list = 0;
-    S->tau_v = -INFINITY;
-    S->tau_i = 0x7fffffff;
+    S->tau = 0ull;
     S->w_eos = 0.f;
+    S->psi_eos = 0.f;
     mbar_fence_init();
   }
   __syncthreads();
   LGASR_TR(0, 0);
   LGASR_TR(1, 0);
 
-  if (tid < kGroupThreads) {
+  if (tid < kCtcThreads) {
     // ======================= ctc group: CTC state of this hypothesis ==================================
     if (d.use_ctc) {
       const int g = tid;
@@ -312,12 +369,13 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
       mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
       LGASR_TR(0, 1);
       float* r_out = d.r[rp ^ 1] + ((long long)row * 2) * Tp;
-      group_ctc_state(bR0, bR1, bA, bB, bC, bD, r_out, has_parent, last == rm.z, olen - 1, T, Tp, g, S->ws, kBarCtc);
+      group_ctc_state(bR0, bR1, bA, bB, bC, bD, r_out, has_parent, step == 1, last == rm.z, olen - 1, T, Tp, g, S->ws,
+                      &S->psi_eos, kBarCtc);
       LGASR_TR(0, 2);
     }
   } else if (mode != kModeFullCtc) {
     // ======================= sel group: fused row stream + exact top-n_sel ============================
-    const int j = tid - kGroupThreads;
+    const int j = tid - kCtcThreads;
     const int wj = j >> 5;
     const int nchunks = (V + CH - 1) / CH;
     const bool tma = sl.tma_rows != 0;
@@ -331,7 +389,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
       const int stage = c % NST;
       const int e0 = c * CH;
       float val[EPT];
-      // ---- values of this thread: elements e0 + 4*(j + 128*i) + u ---------------------------------
+      // ---- values of this thread: elements e0 + 4*(j + kSelGroup*i) + u -----------------------------
       const int n_ch = min(CH, V - e0);
       const float* sb;
       if (tma) {
@@ -347,16 +405,16 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
           if (!src) continue;
           src += rowoff + e0;
           float* dst = arena + tm.slot[k] * CH;
-          for (int i = j; i < n_ch; i += kGroupThreads) dst[i] = __ldg(src + i);
+          for (int i = j; i < n_ch; i += kSelGroup) dst[i] = __ldg(src + i);
         }
-        group_bar(kBarSel);
+        group_bar(kBarSel, kSelGroup);
       }
       {
         float4 acc[EPT / 4];
         if (d.key >= 0) {
           const float* base = sb + tm.slot[d.key] * CH;
 #pragma unroll
-          for (int i = 0; i < EPT / 4; ++i) acc[i] = *reinterpret_cast<const float4*>(base + 4 * (j + kGroupThreads * i));
+          for (int i = 0; i < EPT / 4; ++i) acc[i] = *reinterpret_cast<const float4*>(base + 4 * (j + kSelGroup * i));
         } else {
 #pragma unroll
           for (int i = 0; i < EPT / 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -367,7 +425,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
               const float* base = sb + tm.slot[k] * CH;
 #pragma unroll
               for (int i = 0; i < EPT / 4; ++i) {
-                const float4 sv = *reinterpret_cast<const float4*>(base + 4 * (j + kGroupThreads * i));
+                const float4 sv = *reinterpret_cast<const float4*>(base + 4 * (j + kSelGroup * i));
                 acc[i].x = __fadd_rn(acc[i].x, __fmul_rn(wk, sv.x));
                 acc[i].y = __fadd_rn(acc[i].y, __fmul_rn(wk, sv.y));
                 acc[i].z = __fadd_rn(acc[i].z, __fmul_rn(wk, sv.z));
@@ -394,35 +452,40 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
         }
       }
       // the fused score of eos is needed even when eos is not a pre-beam candidate (:180-181)
-      if (d.key < 0) {
+      if (d.key < 0 && d.eos >= e0 && d.eos < e0 + CH) {
+        const int q = (d.eos - e0) >> 2;
+        if (q % kSelGroup == j) {
+          const int ii = 4 * (q / kSelGroup) + (d.eos & 3);
 #pragma unroll
-        for (int i = 0; i < EPT; ++i)
-          if (e0 + 4 * (j + kGroupThreads * (i >> 2)) + (i & 3) == d.eos) S->w_eos = val[i];
+          for (int i = 0; i < EPT; ++i)
+            if (i == ii) S->w_eos = val[i];
+        }
       }
-      // ---- threshold of the first chunk: at least n_sel elements are >= the k-th largest lane maximum
-      //      of every warp (k = ceil(n_sel / 4)) --------------------------------------------------------
-      if (c == 0) {
-        float mx = -INFINITY;
-        bool any = false;
+      // elements past the end of the vocabulary never qualify: NaN fails every comparison below
+      if (n_ch < CH) {
 #pragma unroll
         for (int i = 0; i < EPT; ++i)
-          if (e0 + 4 * (j + kGroupThreads * (i >> 2)) + (i & 3) < V) {
-            mx = fmaxf(mx, val[i]);
-            any = true;
-          }
-        unsigned cur = any ? f2ord(mx) : 0u;
+          if (4 * (j + kSelGroup * (i >> 2)) + (i & 3) >= n_ch) val[i] = __int_as_float(0x7fc00000);
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < EPT; ++i) mx = fmaxf(mx, val[i]);
+      // ---- threshold of the first chunk: at least n_sel elements are >= the k-th largest lane maximum
+      //      of every warp (k = ceil(n_sel / kSelWarps)) ------------------------------------------------
+      if (c == 0) {
+        unsigned cur = (mx > -INFINITY) ? f2ord(mx) : 0u;
         unsigned kth = 0u;
-        const int kk = (n_sel + kGroupWarps - 1) / kGroupWarps;
+        const int kk = (n_sel + kSelWarps - 1) / kSelWarps;
         for (int r = 0; r < kk; ++r) {
           kth = __reduce_max_sync(FULLMASK, cur);
           const unsigned holders = __ballot_sync(FULLMASK, cur == kth);
           if (lane == __ffs(holders) - 1) cur = 0u;
         }
         if (lane == 0) S->wkth[wj] = kth;
-        group_bar(kBarSel);
+        group_bar(kBarSel, kSelGroup);
         unsigned mn = S->wkth[0];
 #pragma unroll
-        for (int w2 = 1; w2 < kGroupWarps; ++w2) mn = min(mn, S->wkth[w2]);
+        for (int w2 = 1; w2 < kSelWarps; ++w2) mn = min(mn, S->wkth[w2]);
         tau_v = (mn == 0u) ? -INFINITY : ord2f(mn);
         tau_i = 0x7fffffff;
       }
@@ -430,21 +493,44 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
       unsigned pushed = 0u;
       bool first_round = true;
       while (true) {
+        // cheap filter first (one compare per thread), the exact (value, index) test only in warps that pass
+        if (__any_sync(FULLMASK, mx >= tau_v)) {
+          unsigned pmask = 0u;
 #pragma unroll
-        for (int i = 0; i < EPT; ++i) {
-          const int e = e0 + 4 * (j + kGroupThreads * (i >> 2)) + (i & 3);
-          if (e < V && !((pushed >> i) & 1u) && better(val[i], e, tau_v, tau_i)) {
-            const int slot = atomicAdd(&S->pend_cnt, 1);
-            if (slot < kPendCap) {
-              S->pend_val[slot] = val[i];
-              S->pend_idx[slot] = e;
-              pushed |= 1u << i;
-            } else {
-              S->overflow = 1;
+          for (int i = 0; i < EPT; ++i) {
+            const int e = e0 + 4 * (j + kSelGroup * (i >> 2)) + (i & 3);
+            if (better(val[i], e, tau_v, tau_i)) pmask |= 1u << i;
+          }
+          pmask &= ~pushed;
+          const int ct = __popc(pmask);
+          int inc = ct;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(FULLMASK, inc, o);
+            if (lane >= o) inc += v;
+          }
+          const int total = __shfl_sync(FULLMASK, inc, 31);
+          if (total > 0) {
+            int base = 0;
+            if (lane == 31) base = atomicAdd(&S->pend_cnt, total);
+            base = __shfl_sync(FULLMASK, base, 31);
+            int slot = base + inc - ct;
+            unsigned long long* kp = S->keys[S->cur_list] + S->n_top;
+#pragma unroll
+            for (int i = 0; i < EPT; ++i) {
+              if ((pmask >> i) & 1u) {
+                if (slot < kPendCap) {
+                  kp[slot] = pack_key(val[i], e0 + 4 * (j + kSelGroup * (i >> 2)) + (i & 3));
+                  pushed |= 1u << i;
+                } else {
+                  S->overflow = 1;
+                }
+                ++slot;
+              }
             }
           }
         }
-        group_bar(kBarSel);  // also: every thread has read its stage values
+        group_bar(kBarSel, kSelGroup);  // also: every thread has read its stage values
         if (first_round && tma && j == 0 && c + NST < nchunks) {
           fence_proxy_async();
           issue_row_chunk(tm, rowoff, c + NST, CH, NST, V, arena, S);
@@ -453,145 +539,124 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
         const int cnt = S->pend_cnt;
         const int ovf = S->overflow;
         if (cnt == 0) {
-          group_bar(kBarSel);  // nobody may push into the next chunk's list before everyone has read cnt
+          group_bar(kBarSel, kSelGroup);  // nobody may push into the next chunk's list before everyone has read cnt
           break;
         }
         const int cl = S->cur_list;
         const int n_l = S->n_top;
-        const int n_p = cnt < kPendCap ? cnt : kPendCap;
-        const int n = n_l + n_p;
-        const float* lv = S->top_val[cl];
-        const int* li = S->top_idx[cl];
-        float* nv = S->top_val[cl ^ 1];
-        int* ni = S->top_idx[cl ^ 1];
-        for (int e = j; e < n; e += kGroupThreads) {
-          const float ve = e < n_l ? lv[e] : S->pend_val[e - n_l];
-          const int ie = e < n_l ? li[e] : S->pend_idx[e - n_l];
+        const int n = n_l + (cnt < kPendCap ? cnt : kPendCap);
+        const unsigned long long* ks = S->keys[cl];
+        unsigned long long* kn = S->keys[cl ^ 1];
+        for (int e = j; e < n; e += kSelGroup) {
+          const unsigned long long ke = ks[e];
           int rank = 0;
-          for (int o = 0; o < n_l; ++o) rank += better(lv[o], li[o], ve, ie) ? 1 : 0;
-          for (int o = 0; o < n_p; ++o) rank += better(S->pend_val[o], S->pend_idx[o], ve, ie) ? 1 : 0;
-          if (rank < n_sel) {
-            nv[rank] = ve;
-            ni[rank] = ie;
-          }
+#pragma unroll 4
+          for (int o = 0; o < n; ++o) rank += (ks[o] > ke) ? 1 : 0;
+          if (rank < n_sel) kn[rank] = ke;
         }
-        group_bar(kBarSel);
+        group_bar(kBarSel, kSelGroup);
         if (j == 0) {
           const int nt = n < n_sel ? n : n_sel;
           S->n_top = nt;
           S->cur_list = cl ^ 1;
           S->pend_cnt = 0;
           S->overflow = 0;
-          if (nt == n_sel) {
-            S->tau_v = nv[n_sel - 1];
-            S->tau_i = ni[n_sel - 1];
+          S->tau = (nt == n_sel) ? kn[n_sel - 1] : 0ull;
+        }
+        group_bar(kBarSel, kSelGroup);
+        {
+          const unsigned long long tk2 = S->tau;
+          if (tk2) {
+            tau_v = key_val(tk2);
+            tau_i = key_idx(tk2);
           } else {
-            S->tau_v = -INFINITY;
-            S->tau_i = 0x7fffffff;
+            tau_v = -INFINITY;
+            tau_i = 0x7fffffff;
           }
         }
-        group_bar(kBarSel);
-        tau_v = S->tau_v;
-        tau_i = S->tau_i;
         if (!ovf) break;
       }
     }
     LGASR_TR(1, 2);
     // ---- gather the candidates' posterior rows (first group) by TMA ------------------------------------
-    if (mode == kModePreBeam && j == 0) {
-      const int cl = S->cur_list;
+    if (mode == kModePreBeam && wj == 0) {
       const int nt = S->n_top;
-      const int g1 = nt < sl.rows_per_group ? nt : sl.rows_per_group;
-      const uint32_t rb = (uint32_t)Tp * 4u;
-      uint32_t bytes = 0;
-      for (int i = 0; i < g1; ++i) {
-        const int cc = S->top_idx[cl][i];
-        if (cc != d.eos && !(d.eos != d.blank && cc == d.blank)) bytes += rb;
-      }
-      fence_proxy_async();
-      mbar_expect_tx(reinterpret_cast<uint64_t*>(&S->bar_cand), bytes);
-      for (int i = 0; i < g1; ++i) {
-        const int cc = S->top_idx[cl][i];
-        if (cc != d.eos && !(d.eos != d.blank && cc == d.blank))
-          bulk_g2s(arena + (long long)i * Tp, xT_b + (long long)cc * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_cand));
-      }
+      issue_cand_rows(d, S->keys[S->cur_list], 0, nt < sl.rows_per_group ? nt : sl.rows_per_group, xT_b, arena, S, lane);
     }
   }
   __syncthreads();
   LGASR_TR(0, 3);
 
   // ======================= all warps: candidate records ===============================================
-  const int cl = S->cur_list;
   const int n_top = S->n_top;
-  const float* tv = S->top_val[cl];
-  const int* ti = S->top_idx[cl];
+  const unsigned long long* tk = S->keys[S->cur_list];
   const int R = d.R;
   float* c_total = d.cand_total + (long long)row * R;
   int* c_tok = d.cand_tok + (long long)row * R;
   float* c_psi = d.cand_psi + (long long)row * R;
-  constexpr int kWarps = kStepThreads / 32;
 
   if (mode == kModeNoCtc) {
-    for (int jr = tid; jr < d.W; jr += kStepThreads) {
-      float total = -INFINITY;
-      int c = -1;
-      if (jr < n_top) {
-        c = ti[jr];
-        const float wfull = (d.key < 0) ? tv[jr] : fuse_at(tm, rowoff, c);
-        total = __fadd_rn(wfull, hyp_score);
+    if (lane == 0) {
+      for (int jr = warp; jr < d.W; jr += kStepWarps) {
+        float total = -INFINITY;
+        int c = -1;
+        if (jr < n_top) {
+          c = key_idx(tk[jr]);
+          const float wfull = (d.key < 0) ? key_val(tk[jr]) : fuse_at(tm, rowoff, c);
+          total = __fadd_rn(wfull, hyp_score);
+        }
+        c_total[jr] = total;
+        c_tok[jr] = c;
+        c_psi[jr] = 0.f;
       }
-      c_total[jr] = total;
-      c_tok[jr] = c;
-      c_psi[jr] = 0.f;
     }
   } else {
-    const int start = olen > 1 ? olen : 1;
-    const float psi_eos = bA[T - 1];  // r_sum at the end frame (ctc_prefix_score.py:180-181)
+    const float psi_eos = S->psi_eos;  // r_sum at the end frame (ctc_prefix_score.py:180-181)
     const int RPG = sl.rows_per_group;
-    const uint32_t rb = (uint32_t)Tp * 4u;
+    const int nq = Tp >> 2;
+    constexpr float kL2E = 1.4426950408889634f;
     int grp = 0;
     for (int g0 = 0; g0 < n_top; g0 += RPG, ++grp) {
       const int g1 = (g0 + RPG < n_top) ? g0 + RPG : n_top;
       if (g0 > 0) {
         __syncthreads();  // the arena rows of the previous group have been consumed
-        if (tid == 0) {
-          uint32_t bytes = 0;
-          for (int i = g0; i < g1; ++i) {
-            const int cc = ti[i];
-            if (cc != d.eos && !(d.eos != d.blank && cc == d.blank)) bytes += rb;
-          }
-          fence_proxy_async();
-          mbar_expect_tx(reinterpret_cast<uint64_t*>(&S->bar_cand), bytes);
-          for (int i = g0; i < g1; ++i) {
-            const int cc = ti[i];
-            if (cc != d.eos && !(d.eos != d.blank && cc == d.blank))
-              bulk_g2s(arena + (long long)(i - g0) * Tp, xT_b + (long long)cc * Tp, rb,
-                       reinterpret_cast<uint64_t*>(&S->bar_cand));
-          }
-        }
+        if (warp == 0) issue_cand_rows(d, tk, g0, g1, xT_b, arena, S, lane);
       }
-      mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand), (uint32_t)(grp & 1));
-      LGASR_TR(0, 4);
-      for (int jr = g0 + warp; jr < g1; jr += kWarps) {
-        const int c = ti[jr];
-        const float wfull = (d.key < 0) ? tv[jr] : fuse_at(tm, rowoff, c);
+      bool waited = false;
+      for (int jr = g0 + warp; jr < g1; jr += kStepWarps) {
+        const int c = key_idx(tk[jr]);
+        const float wfull = (d.key < 0) ? key_val(tk[jr]) : fuse_at(tm, rowoff, c);
         float psi;
         if (c == d.eos) {
           psi = psi_eos;
         } else if (d.eos != d.blank && c == d.blank) {
           psi = LGASR_LOGZERO;  // :183-185
         } else {
+          if (!waited) {
+            mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand[warp]), (uint32_t)(grp & 1));
+            waited = true;
+            if (jr == 0) LGASR_TR(0, 4);
+          }
           // log psi = logsumexp({phi[t-1] + x[t] : start <= t < T} U {r^n[start-1]})  (:163-171), the way
-          // torch.logsumexp does it: max, sum of exp, log
-          const float* x = arena + (long long)(jr - g0) * Tp;
-          const float* phi = (c == last) ? bD : bA;
-          const float rn0 = (olen == 0) ? x[0] : LGASR_LOGZERO;
+          // torch.logsumexp does it (max, sum of exp, log).  phi is pre-shifted and LGASR_NEG outside
+          // [start, T), so the sum runs over whole float4 rows.
+          const float4* x4 = reinterpret_cast<const float4*>(arena + (long long)(jr - g0) * Tp);
+          const float4* p4 = reinterpret_cast<const float4*>((c == last) ? bR1 : bR0);
+          const float rn0 = (olen == 0) ? arena[(long long)(jr - g0) * Tp] : LGASR_LOGZERO;
           float m = rn0;
-          for (int t = start + lane; t < T; t += 32) m = fmaxf(m, phi[t - 1] + x[t]);
+          for (int q = lane; q < nq; q += 32) {
+            const float4 xv = x4[q], pv = p4[q];
+            m = fmaxf(fmaxf(fmaxf(m, pv.x + xv.x), fmaxf(pv.y + xv.y, pv.z + xv.z)), pv.w + xv.w);
+          }
 #pragma unroll
           for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULLMASK, m, o));
-          float sum = (lane == 0) ? expf(rn0 - m) : 0.f;
-          for (int t = start + lane; t < T; t += 32) sum += expf(phi[t - 1] + x[t] - m);
+          // (e - m) first: the subtraction is exact near the maximum, where the terms matter
+          float sum = (lane == 0) ? exp2f((rn0 - m) * kL2E) : 0.f;
+          for (int q = lane; q < nq; q += 32) {
+            const float4 xv = x4[q], pv = p4[q];
+            sum += exp2f((pv.x + xv.x - m) * kL2E) + exp2f((pv.y + xv.y - m) * kL2E) +
+                   exp2f((pv.z + xv.z - m) * kL2E) + exp2f((pv.w + xv.w - m) * kL2E);
+          }
 #pragma unroll
           for (int o = 16; o >= 1; o >>= 1) sum += __shfl_xor_sync(FULLMASK, sum, o);
           psi = m + logf(sum);
@@ -602,17 +667,21 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
           c_psi[jr] = psi;
         }
       }
+      // a warp that had nothing to wait for in this group still has to consume the barrier phase
+      if (!waited && (g0 + RPG < n_top)) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand[warp]), (uint32_t)(grp & 1));
     }
-    // unused pre-beam slots (fewer than S tokens in the vocabulary) and the eos slot
-    for (int jr = n_top + tid; jr < n_sel; jr += kStepThreads) {
-      c_total[jr] = -INFINITY;
-      c_tok[jr] = -1;
-      c_psi[jr] = 0.f;
+    if (lane == 0) {
+      // unused pre-beam slots (fewer than S tokens in the vocabulary)
+      for (int jr = n_top + warp; jr < n_sel; jr += kStepWarps) {
+        c_total[jr] = -INFINITY;
+        c_tok[jr] = -1;
+        c_psi[jr] = 0.f;
+      }
     }
-    if (warp == kWarps - 1) {
+    if (warp == kStepWarps - 1) {
       // eos is always scored by the CTC scorer (:180-181); skip if it already is a candidate
       bool dup = false;
-      for (int e = lane; e < n_top; e += 32) dup |= (ti[e] == d.eos);
+      for (int e = lane; e < n_top; e += 32) dup |= (key_idx(tk[e]) == d.eos);
       dup = __any_sync(FULLMASK, dup);
       if (lane == 0) {
         float total = -INFINITY;
@@ -629,7 +698,7 @@ __global__ void __launch_bounds__(kStepThreads) k_step(Dev d, Terms tm, StepLaun
 
   // ======================= ticket: the last CTA of the utterance runs the selection ==================
   LGASR_TR(0, 5);
-  __threadfence();
+  if (lane == 0) __threadfence();  // only lane 0 of each warp wrote records
   __syncthreads();
   if (tid == 0) {
     const int old = atomicAdd(d.arrive + b, 1);
