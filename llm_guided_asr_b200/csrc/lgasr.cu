@@ -146,7 +146,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
   if (h->NL == 3) h->NL = 4;
   const int capS = 32 * h->NL;
   h->smem_rows = (size_t)4 * d.Tp * sizeof(float) + (size_t)kRowWarps * capS * 8 + (size_t)capS * 8;
-  h->smem_sel = (size_t)d.W * d.R * 12 + (size_t)d.W * 8;
+  h->smem_sel = (size_t)utt_select_smem_floats(d.W, d.R, d.K + (c->use_ctc ? 1 : 0)) * sizeof(float);
   if (h->smem_rows > 220 * 1024 || h->smem_sel > 220 * 1024) {
     delete h;
     return fail(LGASR_EINVAL, "shared memory need too large (T=%d beam=%d)", d.T, d.W);
@@ -158,14 +158,17 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     h->fused = (d.mode != kModeFullCtc) && !(env && env[0] == '1');
     StepLaunch& sl = h->sl;
     const int K = d.K > 0 ? d.K : 1;
-    // elements per selection thread and chunk: 16 when one scorer matrix is streamed and the row is long
-    h->ept = (K == 1 && d.V > 8 * kSelGroup) ? 16 : 8;
-    sl.CH = h->ept * kSelGroup;
-    const int nchunks = (d.V + sl.CH - 1) / sl.CH;
-    int nst = 6144 / (K * sl.CH);
-    if (nst < 1) nst = 1;
-    if (nst > kMaxStages) nst = kMaxStages;
-    if (nst > nchunks) nst = nchunks;
+    // stage budget: 6144 floats (24 KB).  A row set that fits is ONE chunk; longer rows are streamed through
+    // two stages of half the budget each.
+    const int budget = 6144;
+    const int V4 = (d.V + 3) & ~3;
+    int nst = 1;
+    if ((long long)K * V4 <= budget) {
+      sl.CH = V4;
+    } else {
+      nst = 2;
+      sl.CH = (budget / (2 * K)) & ~3;
+    }
     sl.NST = nst;
     sl.tma_rows = 0;  // decided per step from the pointers
     long long arena = (long long)nst * K * sl.CH;
@@ -173,7 +176,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     if (cand > 6144) cand = 6144;
     if (cand < d.Tp) cand = d.Tp;
     if (d.mode == kModePreBeam && cand > arena) arena = cand;
-    const long long selw = (long long)d.W * d.R * 3 + 2 * d.W;
+    const long long selw = utt_select_smem_floats(d.W, d.R, d.NS);
     if (selw > arena) arena = selw;
     arena = (arena + 3) & ~3LL;
     sl.arena_floats = (int)arena;
@@ -262,13 +265,11 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       }
       if (e == cudaSuccess) cur_rows[h->NL] = h->smem_rows;
     }
-    static size_t cur_step[2] = {0, 0};
-    if (e == cudaSuccess && h->fused && h->smem_step > cur_step[h->ept == 16]) {
-      if (h->ept == 16)
-        e = cudaFuncSetAttribute(k_step<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
-      else
-        e = cudaFuncSetAttribute(k_step<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
-      if (e == cudaSuccess) cur_step[h->ept == 16] = h->smem_step;
+    static size_t cur_step = 0;
+    if (e == cudaSuccess && h->fused && h->smem_step > cur_step) {
+      e = cudaFuncSetAttribute(k_step<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      if (e == cudaSuccess) cur_step = h->smem_step;
     }
     if (e == cudaSuccess && h->smem_sel > cur_sel) {
       e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_sel);
@@ -410,10 +411,10 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st) {
     for (int k = 0; k < tm.K; ++k)
       if (tm.ptr[k]) al = al && ((reinterpret_cast<uintptr_t>(tm.ptr[k]) & 15) == 0);
     sl.tma_rows = al ? 1 : 0;
-    if (h->ept == 16)
-      k_step<16><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
+    if (d.trace)
+      k_step<true><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
     else
-      k_step<8><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
+      k_step<false><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
     LAUNCH_CK();
     if (h->profiling) {
       CK(cudaEventRecord(pe[1], st));

@@ -17,14 +17,22 @@
 
 namespace lgasr {
 
-// m + log(exp(a-m) + exp(b-m)), the two-operand torch.logsumexp (one of the exps is exp(0) = 1)
-// Accurate expf/logf on purpose: r values reach magnitudes of 1e2..1e3 where one fp32 ulp is already ~6e-5,
-// so the 1e-4 score bar only holds if the dominant terms are evaluated like the reference evaluates them
-// (MUFU-approximate exp/log measured 9e-5 off on the bench workload; this form measured 0.0).
+// m + log(exp(a-m) + exp(b-m)), the two-operand torch.logsumexp (one of the exps is exp(0) = 1).
+// Default: MUFU ex2/lg2.  For this composite the hardware approximations are as good as the library calls:
+// the log argument 1 + e lies in [1, 2], where lg2.approx has an ABSOLUTE error <= 2^-22 (1.6e-7 after the
+// ln 2 scale), and the 2-ulp error of ex2.approx enters through d/de log(1+e) <= 1/2 (<= 1.2e-7); expf + logf
+// give ~1.8e-7 worst case for 4x the instructions.  -DLGASR_ACCURATE_LSE selects the library calls.
 __device__ __forceinline__ float lse2(float a, float b) {
-  float m = fmaxf(a, b);
-  float d = fminf(a, b) - m;  // <= 0
+  const float m = fmaxf(a, b);
+  const float d = fminf(a, b) - m;  // <= 0
+#ifdef LGASR_ACCURATE_LSE
   return m + logf(1.0f + expf(d));
+#else
+  float e, l;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(d * 1.4426950408889634f));
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(1.0f + e));
+  return fmaf(l, 0.6931471805599453f, m);
+#endif
 }
 
 // total order used by every selection: larger value first, then smaller index

@@ -346,35 +346,67 @@ __device__ __forceinline__ float key_total(unsigned long long k) {
   return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
-// Selection of one utterance (all kSelThreads threads of a CTA): global top-beam over the candidate
-// records of its running hypotheses (batch_beam, batch_beam_search.py:101-128), hypothesis
-// bookkeeping (:325-363), post_process (:365-429) and end_detect (e2e_asr_common.py:17-48).
-// Reads state [pp], writes state [pp^1].  smem: >= W*R*12 + W*8 bytes (16-byte aligned).
+// Selection of one utterance (all threads of a CTA): global top-beam over the candidate records of its
+// running hypotheses (batch_beam, batch_beam_search.py:101-128), hypothesis bookkeeping (:325-363),
+// post_process (:365-429) and end_detect (e2e_asr_common.py:17-48).
+// Reads state [pp], writes state [pp^1].  smem: >= utt_select_smem_floats(W, R, NS) floats, 16-byte aligned.
+// Every global operand whose address is known up front (records, the parents' fields, the ended-pool
+// scalars) is requested in ONE batch of loads before the first barrier, so the whole selection costs a
+// single global round trip plus the scattered reads of the chosen tokens' full-scorer scores.
+constexpr int kSelListCap = 256;  // survivors of the row-maximum prefilter of utt_select
+__host__ __device__ inline long long utt_select_smem_floats(int W, int R, int NS) {
+  // records (key u64 + psi) | sel, dest | parents' fields | row maxima (u64) | survivor list (key u64 + index) | scalars
+  return (long long)W * R * 3 + 2LL * W + (long long)W * (3 + NS) + 2LL * W + 3LL * kSelListCap + 8;
+}
+
 __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b, int pp, int step, float* smem) {
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, nthr = blockDim.x;
   const int n_run = d.n_run[pp][b];
-  const int R = d.R, W = d.W;
+  const int R = d.R, W = d.W, NS = d.NS;
   const int n_rec_row = (d.mode == kModePreBeam) ? d.S + 1 : d.W;
   const int nrec = n_run * n_rec_row;
   // packed records: key = (ordered total << 32) | ~(h*V + tok): larger key = higher total, then lower flat index
   unsigned long long* r_key = reinterpret_cast<unsigned long long*>(smem);  // [W*R]   0 = invalid
   float* r_psi = reinterpret_cast<float*>(r_key + W * R);                   // [W*R]
   int* sel = reinterpret_cast<int*>(r_psi + W * R);                         // [W] record index per rank
-  int* dest = sel + W;  // [W] >=0 running idx, -1-e ended idx e, INT_MIN dropped
-  __shared__ int sh_nsel;
-  __shared__ unsigned long long sh_redk[kSelThreads / 32];
-  __shared__ int sh_rede[kSelThreads / 32];
+  int* dest = sel + W;             // [W] >=0 running idx, -1-e ended idx e, INT_MIN dropped
+  int* p_slot = dest + W;          // [W] parents: slot in the best list of the step that made them
+  int* p_last = p_slot + W;        // [W] parents: last token
+  float* p_sprev = reinterpret_cast<float*>(p_last + W);  // [W]
+  float* p_scores = p_sprev + W;   // [W][NS]
+  // 8-byte aligned tail: W*R*3 + 2W + 3W + W*NS floats precede it; pad to an even count
+  float* tail = p_scores + W * NS;
+  if ((tail - smem) & 1) ++tail;
+  unsigned long long* rowmax = reinterpret_cast<unsigned long long*>(tail);  // [W]
+  unsigned long long* c_key = rowmax + W;                                    // [kSelListCap]
+  int* c_e = reinterpret_cast<int*>(c_key + kSelListCap);                    // [kSelListCap]
+  int* sh_nsel = c_e + kSelListCap;
+  int* sh_cnt = sh_nsel + 1;
   const int cur_len = d.cur_len[pp][b];
   const int maxlen = d.maxlen[b], minlen = d.minlen[b];
-  // scalars of the serial part, fetched early (only this utterance's selection ever writes them)
+  const bool last = (step == maxlen - 1);
+  const int new_len = cur_len + 1 + (last ? 1 : 0);
+  float* bbl = d.best_by_len + (long long)b * (d.Lcap + 2);
+  // scalars of the serial part (only this utterance's selection ever writes them)
   int n_end0 = 0;
-  float best_all0 = 0.f;
+  float best_all0 = 0.f, bbl_new0 = 0.f, bbl_m[3] = {-INFINITY, -INFINITY, -INFINITY};
   if (tid == 0) {
     n_end0 = d.n_ended[b];
     best_all0 = d.best_all[b];
+    bbl_new0 = bbl[new_len];
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+      const int len = step - m;
+      if (len >= 0 && len <= d.Lcap + 1) bbl_m[m] = bbl[len];
+    }
   }
-
-  for (int e = tid; e < nrec; e += kSelThreads) {
+  // row-maximum prefilter: with W running rows, the W row maxima are W distinct records, so nothing below
+  // their minimum can be among the W best; typically ~2W of the W*(S+1) records survive
+  const bool prefilter = (n_run >= W) && (nrec <= 2 * nthr);
+  if (tid < W) rowmax[tid] = 0ull;
+  if (tid == 0) *sh_cnt = 0;
+  if (prefilter) __syncthreads();
+  for (int e = tid; e < nrec; e += nthr) {
     const int h = e / n_rec_row, j = e - h * n_rec_row;
     const long long o = (long long)(b * W + h) * R + j;
     const int tok = __ldcg(d.cand_tok + o);  // written by other CTAs of this launch: read through L2
@@ -382,28 +414,80 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
     r_psi[e] = __ldcg(d.cand_psi + o);
     unsigned u = __float_as_uint(tot + 0.0f);
     u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-    r_key[e] = tok >= 0 ? (((unsigned long long)u << 32) | (unsigned)(~(h * d.V + tok))) : 0ull;
+    const unsigned long long ke = tok >= 0 ? (((unsigned long long)u << 32) | (unsigned)(~(h * d.V + tok))) : 0ull;
+    r_key[e] = ke;
+    if (prefilter && ke) atomicMax(rowmax + h, ke);
+  }
+  for (int i = tid; i < n_run * (3 + NS); i += nthr) {
+    const int h = i / (3 + NS), f = i - h * (3 + NS);
+    const int prow = b * W + h;
+    if (f == 0) p_slot[h] = d.run_slot[pp][prow];
+    else if (f == 1) p_last[h] = d.rmeta[pp][prow].y;
+    else if (f == 2) p_sprev[h] = d.s_prev[pp][prow];
+    else p_scores[h * NS + (f - 3)] = d.scores[pp][(long long)prow * NS + (f - 3)];
   }
   if (tid < W) sel[tid] = -1;
   __syncthreads();
-  if (nrec <= 2 * kSelThreads) {
-    // rank by counting
-    for (int e = tid; e < nrec; e += kSelThreads) {
+  bool ranked = false;
+  if (prefilter) {
+    unsigned long long tau = ~0ull;
+    for (int h = 0; h < W; ++h) {
+      const unsigned long long rmx = rowmax[h];
+      tau = rmx < tau ? rmx : tau;
+    }
+    for (int e = tid; e < nrec; e += nthr) {
+      const unsigned long long ke = r_key[e];
+      if (ke != 0ull && ke >= tau) {
+        const int slot = atomicAdd(sh_cnt, 1);
+        if (slot < kSelListCap) {
+          c_key[slot] = ke;
+          c_e[slot] = e;
+        }
+      }
+    }
+    __syncthreads();
+    const int n = *sh_cnt;
+    if (n <= kSelListCap) {
+      for (int i = tid; i < n; i += nthr) {
+        const unsigned long long ke = c_key[i];
+        int rank = 0;
+#pragma unroll 4
+        for (int o = 0; o < n; ++o) rank += (c_key[o] > ke) ? 1 : 0;
+        if (rank < W) sel[rank] = c_e[i];
+      }
+      ranked = true;
+      __syncthreads();
+    }
+  }
+  if (ranked) {
+  } else if (nrec <= 2 * nthr) {
+    // rank by counting (two keys per shared-memory load)
+    const ulonglong2* k2 = reinterpret_cast<const ulonglong2*>(r_key);
+    const int n2 = nrec >> 1;
+    for (int e = tid; e < nrec; e += nthr) {
       const unsigned long long ke = r_key[e];
       if (ke == 0ull) continue;
       int rank = 0;
 #pragma unroll 4
-      for (int o = 0; o < nrec; ++o) rank += (r_key[o] > ke) ? 1 : 0;
+      for (int o = 0; o < n2; ++o) {
+        const ulonglong2 kk = k2[o];
+        rank += (kk.x > ke) ? 1 : 0;
+        rank += (kk.y > ke) ? 1 : 0;
+      }
+      if (nrec & 1) rank += (r_key[nrec - 1] > ke) ? 1 : 0;
       if (rank < W) sel[rank] = e;
     }
     __syncthreads();
   } else {
     // wide beams: W rounds of block arg-best (each round takes the best record below the previous pick)
+    __shared__ unsigned long long sh_redk[32];
+    __shared__ int sh_rede[32];
+    const int nw = nthr >> 5;
     unsigned long long pk = ~0ull;
     for (int r = 0; r < W; ++r) {
       unsigned long long bk = 0ull;
       int be = -1;
-      for (int e = tid; e < nrec; e += kSelThreads) {
+      for (int e = tid; e < nrec; e += nthr) {
         const unsigned long long ke = r_key[e];
         if (ke != 0ull && ke < pk && ke > bk) {
           bk = ke;
@@ -426,7 +510,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
       __syncthreads();
       bk = sh_redk[0];
       be = sh_rede[0];
-      for (int w = 1; w < kSelThreads / 32; ++w) {
+      for (int w = 1; w < nw; ++w) {
         if (sh_redk[w] > bk) {
           bk = sh_redk[w];
           be = sh_rede[w];
@@ -440,23 +524,20 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
   }
 
   if (tid == 0) {
-    const bool last = (step == maxlen - 1);
     int nsel = 0;
     while (nsel < W && sel[nsel] >= 0) ++nsel;
     int nrun_new = 0;
     int n_end = n_end0;
     float best_all = best_all0;
-    float* bbl = d.best_by_len + (long long)b * (d.Lcap + 2);
-    const int new_len = cur_len + 1 + (last ? 1 : 0);
     float best_new = -INFINITY;  // best ended score of this step: all of them have length new_len
     for (int j = 0; j < nsel; ++j) {
-      int e = sel[j];
-      int tok = (int)(~(unsigned)r_key[e]) % d.V;
-      bool is_eos = last || tok == d.eos;
+      const int e = sel[j];
+      const int tok = (int)(~(unsigned)r_key[e]) % d.V;
+      const bool is_eos = last || tok == d.eos;
       if (is_eos) {
         if (step >= minlen && n_end < d.Ecap) {
           dest[j] = -1 - n_end;
-          float sc = key_total(r_key[e]);
+          const float sc = key_total(r_key[e]);
           d.end_score[(long long)b * d.Ecap + n_end] = sc;
           d.end_meta[(long long)b * d.Ecap + n_end] = make_int4(step, j, new_len, last ? 1 : 0);
           if (sc > best_new) best_new = sc;
@@ -470,31 +551,28 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
     }
     if (best_new > -INFINITY) {
       if (best_new > best_all) best_all = best_new;
-      if (best_new > bbl[new_len]) bbl[new_len] = best_new;
+      if (best_new > bbl_new0) bbl[new_len] = best_new;
       d.n_ended[b] = n_end;
       d.best_all[b] = best_all;
     }
-    // end detection (e2e_asr_common.py:17-48): lengths step, step-1, step-2
+    // end detection (e2e_asr_common.py:17-48): lengths step, step-1, step-2 (none of them is new_len)
     bool fin = (nrun_new == 0) || last;
     if (!fin && d.end_detect && n_end > 0) {
       int count = 0;
+#pragma unroll
       for (int m = 0; m < 3; ++m) {
-        int len = step - m;
-        if (len >= 0 && len <= d.Lcap + 1) {
-          float bs = bbl[len];
-          if (bs > -INFINITY && ((double)bs - (double)best_all) < d.d_end) ++count;
-        }
+        const float bs = bbl_m[m];
+        if (bs > -INFINITY && ((double)bs - (double)best_all) < d.d_end) ++count;
       }
       if (count == 3) fin = true;
     }
     d.n_run[pp ^ 1][b] = nrun_new;
     d.cur_len[pp ^ 1][b] = cur_len + 1;
     d.done[pp ^ 1][b] = fin ? 1 : 0;
-    sh_nsel = nsel;
+    *sh_nsel = nsel;
   }
   __syncthreads();
-  const int nsel = sh_nsel;
-  const int NS = d.NS;
+  const int nsel = *sh_nsel;
   // per-hypothesis fields
   if (tid < nsel) {
     const int j = tid;
@@ -506,7 +584,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
     const float psi = r_psi[e];
     // trellis
     const long long bpo = ((long long)b * d.maxlen_cap + step) * W + j;
-    d.bp_par[bpo] = d.run_slot[pp][prow];
+    d.bp_par[bpo] = p_slot[h];
     d.bp_tok[bpo] = tok;
     const int dj = dest[j];
     float* sc_out = nullptr;
@@ -515,7 +593,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
       d.score[pp ^ 1][nrow] = total;
       d.s_prev[pp ^ 1][nrow] = psi;
       d.run_slot[pp ^ 1][nrow] = j;
-      d.rmeta[pp ^ 1][nrow] = make_int4(h, tok, d.rmeta[pp][prow].y, 0);
+      d.rmeta[pp ^ 1][nrow] = make_int4(h, tok, p_last[h], 0);
       d.step_parent[nrow] = h;
       d.step_tok[nrow] = tok;
       sc_out = d.scores[pp ^ 1] + (long long)nrow * NS;
@@ -523,18 +601,18 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
       sc_out = d.end_scores + ((long long)b * d.Ecap + (-1 - dj)) * NS;
     }
     if (sc_out) {
-      const float* sc_in = d.scores[pp] + (long long)prow * NS;
+      const float* sc_in = p_scores + h * NS;
       const long long rowoff = (long long)prow * tm.ld;
       for (int k = 0; k < tm.K; ++k) {
-        float s = tm.ptr[k] ? __ldg(tm.ptr[k] + rowoff + tok) : tm.cst[k];
+        const float s = tm.ptr[k] ? __ldg(tm.ptr[k] + rowoff + tok) : tm.cst[k];
         sc_out[k] = __fadd_rn(sc_in[k], s);
       }
-      if (d.use_ctc) sc_out[tm.K] = __fadd_rn(sc_in[tm.K], __fsub_rn(psi, d.s_prev[pp][prow]));
+      if (d.use_ctc) sc_out[tm.K] = __fadd_rn(sc_in[tm.K], __fsub_rn(psi, p_sprev[h]));
     }
   }
   // next yseq rows of the running hypotheses
   const int warp = tid >> 5, lane = tid & 31;
-  for (int j = warp; j < nsel; j += kSelThreads / 32) {
+  for (int j = warp; j < nsel; j += nthr >> 5) {
     const int dj = dest[j];
     if (dj < 0) continue;
     const int e = sel[j];

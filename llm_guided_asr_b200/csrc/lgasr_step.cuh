@@ -25,13 +25,13 @@ namespace lgasr {
 constexpr int kStepThreads = 256;
 constexpr int kCtcWarps = 2, kCtcThreads = 32 * kCtcWarps;    // warps 0-1
 constexpr int kSelWarps = 6, kSelGroup = 32 * kSelWarps;       // warps 2-7
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 2;
 constexpr int kPendCap = 256;
 constexpr int kTopCap = 128;  // == LGASR_MAX_PREBEAM
 constexpr int kStepWarps = kStepThreads / 32;
 
 struct StepLaunch {
-  int CH;              // floats per chunk per term (EPT * kSelGroup)
+  int CH;              // floats per chunk per term (multiple of 4)
   int NST;             // stages in flight
   int tma_rows;        // 1: full-scorer rows are 16-byte aligned -> bulk copies; 0: plain loads
   int arena_floats;    // union buffer: row stages | candidate rows | selection scratch
@@ -93,13 +93,13 @@ __device__ __forceinline__ int key_idx(unsigned long long k) { return (int)(~(un
 
 
 // ---- group affine scan ------------------------------------------------------------------------------
-// y[t] = lse2(y[t-1] + a[t], b(t)) for t in [start, T), y[start-1] = y0 (the recursion of
-// ctc_prefix_score.py:155-160) by the kCtcThreads threads of the ctc group.  a, y: shared memory;
-// b(t): functor evaluated once per frame by the thread that owns the frame.
-// g: thread index in the group; ws: 2*kCtcWarps floats of shared scratch.  Ends with a group barrier.
-template <typename BF>
-__device__ __forceinline__ void group_affine_scan(const float* a, float* y, BF bfun, int start, int T, float y0, int g,
-                                                  float* ws, int bar_id) {
+// y[t] = lse2(y[t-1] + a[t], b[t]) for t in [start, T), y[start-1] = y0 (the recursion of
+// ctc_prefix_score.py:155-160) by the kCtcThreads threads of the ctc group.  a, b, y: shared memory (b may
+// alias y).  g: thread index in the group; ws: 2*kCtcWarps floats of shared scratch.  Ends with a group
+// barrier.  Deliberately ONE out-of-line copy with rolled loops: the step kernel must stay small enough for
+// the instruction cache (straight-line code runs at fetch speed, not at issue speed).
+__device__ __noinline__ void group_affine_scan(const float* a, const float* b, float* y, int start, int T, float y0, int g,
+                                               float* ws, int bar_id) {
   const int n = T - start;
   if (n <= 0) return;  // group-uniform
   const int lane = g & 31, w = g >> 5;
@@ -111,19 +111,20 @@ __device__ __forceinline__ void group_affine_scan(const float* a, float* y, BF b
   if (s1 > T) s1 = T;
   // pass 1: local recursion from the scan identity
   float cur = LGASR_NEG, A = 0.f;
+#pragma unroll 1
   for (int t = s0; t < s1; ++t) {
     const float at = a[t];
-    cur = lse2(cur + at, bfun(t));
+    cur = lse2(cur + at, b[t]);
     y[t] = cur;
     A += at;
   }
   // inclusive scan of the segment summaries inside the warp: (A1,B1) then (A2,B2) = (A1+A2, lse2(B1+A2, B2))
   float SA = A, SB = cur;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const float pa = __shfl_up_sync(FULLMASK, SA, d);
-    const float pb = __shfl_up_sync(FULLMASK, SB, d);
-    if (lane >= d) {
+#pragma unroll 1
+  for (int dd = 1; dd < 32; dd <<= 1) {
+    const float pa = __shfl_up_sync(FULLMASK, SA, dd);
+    const float pb = __shfl_up_sync(FULLMASK, SB, dd);
+    if (lane >= dd) {
       SB = lse2(pb + SA, SB);
       SA = pa + SA;
     }
@@ -139,18 +140,18 @@ __device__ __forceinline__ void group_affine_scan(const float* a, float* y, BF b
     eb = LGASR_NEG;
   }
   group_bar(bar_id, kCtcThreads);
-  // summaries of the preceding warps, then this thread's exclusive prefix inside the warp
-  float PA = 0.f, PB = LGASR_NEG;
-  for (int i = 0; i < w; ++i) {
-    const float wa = ws[i], wb = ws[kCtcWarps + i];
-    PB = lse2(PB + wa, wb);
-    PA += wa;
+  // summaries of the preceding warps followed by this thread's exclusive prefix inside the warp
+  float XA = 0.f, XB = LGASR_NEG;
+#pragma unroll 1
+  for (int i = 0; i <= w; ++i) {
+    const float wa = (i < w) ? ws[i] : ea, wb = (i < w) ? ws[kCtcWarps + i] : eb;
+    XB = lse2(XB + wa, wb);
+    XA += wa;
   }
-  const float XA = PA + ea;
-  const float XB = lse2(PB + ea, eb);
   const float yin = (g == 0) ? y0 : lse2(y0 + XA, XB);
   // pass 2: fix-up (independent iterations)
   float run = 0.f;
+#pragma unroll 1
   for (int t = s0; t < s1; ++t) {
     run += a[t];
     y[t] = lse2(yin + run, y[t]);
@@ -173,7 +174,7 @@ __device__ __forceinline__ void group_affine_scan(const float* a, float* y, BF b
 __device__ __forceinline__ void group_ctc_state(float* bR0, float* bR1, const float* bA, float* bB, const float* bC,
                                                 float* bD, float* __restrict__ r_out, int has_parent, int par_initial,
                                                 int same, int olen_par, int T, int Tp, int g, float* ws, float* psi_eos,
-                                                int bar_id) {
+                                                int bar_id, long long* tr) {
   const int start = olen_par > 1 ? olen_par : 1;           // first frame of the recursion that makes this state
   const int pstart = olen_par + 1 > 1 ? olen_par + 1 : 1;  // max(olen, 1) of this hypothesis
   float rn0 = LGASR_LOGZERO;
@@ -181,19 +182,21 @@ __device__ __forceinline__ void group_ctc_state(float* bR0, float* bR1, const fl
     const int start_par = olen_par - 1 > 1 ? olen_par - 1 : 1;  // the parent's own recursion start
     rn0 = (olen_par == 0) ? bA[0] : LGASR_LOGZERO;               // r[start-1, 0]  (:128-129)
     // r^n: a = x_tok, b[t] = phi_parent[t-1] + x_tok[t]; phi = r_sum, or r^b for a repeated token (:131-140)
-    group_affine_scan(
-        bA, bB,
-        [&](int t) {
-          const int u = t - 1;
-          float phi = bR1[u];
-          if (same && !par_initial) phi = (u >= start_par) ? bR1[u - 1] + bC[u] : LGASR_LOGZERO;
-          return phi + bA[t];
-        },
-        start, T, rn0, g, ws, bar_id);
+#pragma unroll 1
+    for (int t = start + g; t < T; t += kCtcThreads) {
+      const int u = t - 1;
+      float phi = bR1[u];
+      if (same && !par_initial) phi = (u >= start_par) ? bR1[u - 1] + bC[u] : LGASR_LOGZERO;
+      bB[t] = phi + bA[t];
+    }
+    group_bar(bar_id, kCtcThreads);
+    group_affine_scan(bA, bB, bB, start, T, rn0, g, ws, bar_id);
+    if (tr && g == 0) tr[8] = clock64();
     // r_sum: a = x_blank, b[t] = r^n[t]   (s_t = lse2(r^b_t, r^n_t), r^b_t = s_{t-1} + x_blank[t])
-    group_affine_scan(
-        bC, bD, [&](int t) { return bB[t]; }, start, T, rn0, g, ws, bar_id);
+    group_affine_scan(bC, bB, bD, start, T, rn0, g, ws, bar_id);
+    if (tr && g == 0) tr[9] = clock64();
   }
+#pragma unroll 1
   for (int u = g; u <= Tp; u += kCtcThreads) {
     const int t = u - 1;  // state of frame t
     float rn = LGASR_LOGZERO, rs = LGASR_LOGZERO, rb = LGASR_LOGZERO;
@@ -234,12 +237,12 @@ __device__ __forceinline__ void group_ctc_state(float* bR0, float* bR1, const fl
 
 // ---- shared-memory header of k_step -------------------------------------------------------------------
 struct __align__(16) StepSmem {
+  unsigned long long keys[2][kTopCap + kPendCap];  // [cur]: sorted top list (n_top) followed by the pending pushes
   unsigned long long bar_full[kMaxStages];  // full-scorer row stages
   unsigned long long bar_ctc;               // parent state + token row + blank row
   unsigned long long bar_cand[kStepWarps];  // candidate rows, one barrier per consuming warp
-  unsigned long long keys[2][kTopCap + kPendCap];  // [cur]: sorted top list (n_top) followed by the pending pushes
-  int pend_cnt, overflow, n_top, cur_list;
-  unsigned long long tau;  // push threshold (key of the n_sel-th best so far; 0 = none)
+  int pend_cnt[2], overflow[2];             // double-buffered by merge iteration (see the sel group)
+  int n_top, cur_list;
   float w_eos, psi_eos;
   int last_flag, pad0;
   float ws[2 * kCtcWarps];
@@ -249,11 +252,17 @@ struct __align__(16) StepSmem {
 // debug time line: stamp i of group grp (0 ctc / all, 1 sel) of this CTA
 #define LGASR_TR(grp, i)                                                                       \
   do {                                                                                          \
-    if (d.trace && tid == ((grp) ? kCtcThreads : 0))                                            \
+    if (TR && tid == ((grp) ? kCtcThreads : 0))                                                 \
       d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2 + (grp)) * 16 + (i)] = clock64(); \
   } while (0)
 
 constexpr int kBarCtc = 1, kBarSel = 2;  // named barriers of the two groups (0 = __syncthreads)
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 // issue the TMA copies of chunk c of this hypothesis' full-scorer rows into its stage
 __device__ __forceinline__ void issue_row_chunk(const Terms& tm, long long rowoff, int c, int CH, int NST, int V, float* arena,
@@ -293,20 +302,51 @@ __device__ __forceinline__ void issue_cand_rows(const Dev& d, const unsigned lon
   }
 }
 
-template <int EPT>
+// fused value of the 4 consecutive vocabulary entries at float offset 4*q of the staged chunk `sb`
+// ([nptr][CH] floats): sum_k w_k * s_k in the reference's fp32 order (batch_beam_search.py:279-300), or the
+// raw scores of the pre-beam key term (beam_search.py:302-308 with pre_beam_score_key != "full").
+__device__ __forceinline__ float4 fused4(const Terms& tm, const float* sb, int CH, int key, int q) {
+  if (key >= 0) return *reinterpret_cast<const float4*>(sb + tm.slot[key] * CH + 4 * q);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+  for (int k = 0; k < tm.K; ++k) {
+    const float wk = tm.w[k];
+    if (tm.ptr[k]) {
+      const float4 sv = *reinterpret_cast<const float4*>(sb + tm.slot[k] * CH + 4 * q);
+      acc.x = __fadd_rn(acc.x, __fmul_rn(wk, sv.x));
+      acc.y = __fadd_rn(acc.y, __fmul_rn(wk, sv.y));
+      acc.z = __fadd_rn(acc.z, __fmul_rn(wk, sv.z));
+      acc.w = __fadd_rn(acc.w, __fmul_rn(wk, sv.w));
+    } else {
+      const float cv = __fmul_rn(wk, tm.cst[k]);
+      acc.x = __fadd_rn(acc.x, cv);
+      acc.y = __fadd_rn(acc.y, cv);
+      acc.z = __fadd_rn(acc.z, cv);
+      acc.w = __fadd_rn(acc.w, cv);
+    }
+  }
+  return acc;
+}
+
+template <bool TR>
 __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepLaunch sl, int pp, int rp, int step) {
   const int b = blockIdx.y, h = blockIdx.x;
   const int tid = threadIdx.x;
-  {
-    const int done = d.done[pp][b], nr = d.n_run[pp][b];
-    if (done || h >= nr) {
-      if (h == 0 && tid == 0 && (done || nr <= 0)) utt_carry_done(d, b, pp);
-      return;
-    }
+  const int W = d.W, V = d.V, Tp = d.Tp;
+  const int row = b * W + h;
+  // per-hypothesis metadata: one batch of independent loads (rows h >= n_run hold stale but valid memory)
+  const int done = d.done[pp][b], n_run = d.n_run[pp][b];
+  const int T = d.xlen[b];
+  const int cur_len = d.cur_len[pp][b];
+  const int4 rm = d.rmeta[pp][row];  // parent slot, last token, parent's last token
+  const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
+  const float hyp_score = d.score[pp][row];
+  if (done || h >= n_run) {
+    if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
+    return;
   }
   extern __shared__ __align__(16) unsigned char smem_raw[];
   StepSmem* S = reinterpret_cast<StepSmem*>(smem_raw);
-  const int Tp = d.Tp, W = d.W, V = d.V;
   float* bR0 = reinterpret_cast<float*>(smem_raw + sizeof(StepSmem));
   float* bR1 = bR0 + Tp;
   float* bA = bR1 + Tp;
@@ -314,38 +354,49 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   float* bC = bB + Tp;
   float* bD = bC + Tp;
   float* arena = bD + Tp;
-  constexpr int CH = EPT * kSelGroup;
-  const int NST = sl.NST;
+  const int CH = sl.CH, NST = sl.NST;
+  const int nchunks = (V + CH - 1) / CH;
+  const bool tma = sl.tma_rows != 0;
 
   const int lane = tid & 31, warp = tid >> 5;
-  const int row = b * W + h;
   const long long rowoff = (long long)row * tm.ld;
-  const int n_run = d.n_run[pp][b];
-  const int T = d.xlen[b];
-  const int cur_len = d.cur_len[pp][b];
   const int olen = cur_len - 1;
-  const int4 rm = d.rmeta[pp][row];  // parent slot, last token, parent's last token
   const int last = rm.y;
-  const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
-  const float hyp_score = d.score[pp][row];
   const float* xT_b = d.xT + (long long)b * V * Tp;
   const int mode = d.mode;
   const int n_sel = (mode == kModePreBeam) ? d.S : d.W;
+  const int has_parent = rm.x >= 0;
 
+  // the two issuing threads initialise their own mbarriers and start their TMA copies before the CTA barrier
   if (tid == 0) {
+    mbar_init(reinterpret_cast<uint64_t*>(&S->bar_ctc), 1);
+    mbar_fence_init();
+    if (d.use_ctc) {
+      const float* r_par = d.r[rp] + ((long long)(b * W + (has_parent ? rm.x : h)) * 2) * Tp;
+      const uint32_t rb = (uint32_t)Tp * 4u;
+      mbar_expect_tx(reinterpret_cast<uint64_t*>(&S->bar_ctc), has_parent ? 4u * rb : 2u * rb);
+      bulk_g2s(bR0, r_par, 2u * rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
+      if (has_parent) {
+        bulk_g2s(bA, xT_b + (long long)last * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
+        bulk_g2s(bC, xT_b + (long long)d.blank * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
+      }
+    }
+  } else if (tid == kCtcThreads) {
 #pragma unroll
     for (int i = 0; i < kMaxStages; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_full[i]), 1);
-    mbar_init(reinterpret_cast<uint64_t*>(&S->bar_ctc), 1);
 #pragma unroll
     for (int i = 0; i < kStepWarps; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_cand[i]), 1);
-    S->pend_cnt = 0;
-    S->overflow = 0;
+    S->pend_cnt[0] = S->pend_cnt[1] = 0;
+    S->overflow[0] = S->overflow[1] = 0;
     S->n_top = 0;
     S->cur_list = 0;
-    S->tau = 0ull;
     S->w_eos = 0.f;
     S->psi_eos = 0.f;
     mbar_fence_init();
+    if (tma && mode != kModeFullCtc) {
+      const int pre = nchunks < NST ? nchunks : NST;
+      for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
+    }
   }
   __syncthreads();
   LGASR_TR(0, 0);
@@ -354,235 +405,207 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   if (tid < kCtcThreads) {
     // ======================= ctc group: CTC state of this hypothesis ==================================
     if (d.use_ctc) {
-      const int g = tid;
-      const int has_parent = rm.x >= 0;
-      if (g == 0) {
-        const float* r_par = d.r[rp] + ((long long)(b * W + (has_parent ? rm.x : h)) * 2) * Tp;
-        const uint32_t rb = (uint32_t)Tp * 4u;
-        mbar_expect_tx(reinterpret_cast<uint64_t*>(&S->bar_ctc), has_parent ? 4u * rb : 2u * rb);
-        bulk_g2s(bR0, r_par, 2u * rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
-        if (has_parent) {
-          bulk_g2s(bA, xT_b + (long long)last * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
-          bulk_g2s(bC, xT_b + (long long)d.blank * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
-        }
-      }
       mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
       LGASR_TR(0, 1);
       float* r_out = d.r[rp ^ 1] + ((long long)row * 2) * Tp;
-      group_ctc_state(bR0, bR1, bA, bB, bC, bD, r_out, has_parent, step == 1, last == rm.z, olen - 1, T, Tp, g, S->ws,
-                      &S->psi_eos, kBarCtc);
+      group_ctc_state(bR0, bR1, bA, bB, bC, bD, r_out, has_parent, step == 1, last == rm.z, olen - 1, T, Tp, tid, S->ws,
+                      &S->psi_eos, kBarCtc, TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
       LGASR_TR(0, 2);
     }
   } else if (mode != kModeFullCtc) {
     // ======================= sel group: fused row stream + exact top-n_sel ============================
+    // Two sweeps over each staged chunk: lane maxima -> threshold (only while the list is not full), then
+    // push everything above the threshold into a pending list (warp-aggregated shared atomics) and merge
+    // by rank counting on packed (value, ~index) keys.  A pending-list overflow (degenerate rows, e.g. all
+    // scores equal) is handled by extra rounds over the same chunk with the tightened threshold.
     const int j = tid - kCtcThreads;
     const int wj = j >> 5;
-    const int nchunks = (V + CH - 1) / CH;
-    const bool tma = sl.tma_rows != 0;
-    if (tma && j == 0) {
-      const int pre = nchunks < NST ? nchunks : NST;
-      for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
-    }
-    float tau_v = -INFINITY;
-    int tau_i = 0x7fffffff;
+    const int key = d.key;
+    const int srows = tm.nptr > 0 ? tm.nptr : 1;
+    int cur = 0, n_top = 0, it = 0;
+    unsigned long long tau = 0ull;  // key of the n_sel-th best so far (0 = list not full)
     for (int c = 0; c < nchunks; ++c) {
-      const int stage = c % NST;
+      const int stage = tma ? c % NST : 0;
       const int e0 = c * CH;
-      float val[EPT];
-      // ---- values of this thread: elements e0 + 4*(j + kSelGroup*i) + u -----------------------------
       const int n_ch = min(CH, V - e0);
-      const float* sb;
+      const int nq = (n_ch + 3) >> 2;
+      float* sb = arena + (long long)stage * srows * CH;
       if (tma) {
         mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[stage]), (uint32_t)((c / NST) & 1));
-        sb = arena + (long long)stage * tm.nptr * CH;
-        if (c == 0) LGASR_TR(1, 1);
       } else {
         // rows that are not 16-byte aligned: the group stages the chunk with plain loads
-        sb = arena;
 #pragma unroll 1
         for (int k = 0; k < tm.K; ++k) {
           const float* src = tm.ptr[k];
           if (!src) continue;
           src += rowoff + e0;
-          float* dst = arena + tm.slot[k] * CH;
+          float* dst = sb + tm.slot[k] * CH;
           for (int i = j; i < n_ch; i += kSelGroup) dst[i] = __ldg(src + i);
         }
         group_bar(kBarSel, kSelGroup);
       }
-      {
-        float4 acc[EPT / 4];
-        if (d.key >= 0) {
-          const float* base = sb + tm.slot[d.key] * CH;
-#pragma unroll
-          for (int i = 0; i < EPT / 4; ++i) acc[i] = *reinterpret_cast<const float4*>(base + 4 * (j + kSelGroup * i));
+      if (c == 0) LGASR_TR(1, 1);
+      // ---- sweep 1: fuse the K terms in place (term-major, so the fp32 order is the reference's
+      //      ((0 + w0*s0) + w1*s1) + ..., batch_beam_search.py:279-300) and take the lane maxima.
+      //      Thread j owns float4s j, j+128, ...: it only ever overwrites what it alone reads. ------------
+      float4* fz = reinterpret_cast<float4*>(key >= 0 ? sb + tm.slot[key] * CH : sb);
+      float mx = -INFINITY;
+      const bool one_term = (key < 0) && (tm.K == 1) && (tm.nptr == 1) && ((n_ch & 3) == 0);
+      if (one_term) {  // the common shape (decoder only): w0 * s0, no tail
+        const float w0 = tm.w[0];
+#pragma unroll 2
+        for (int q = j; q < nq; q += kSelGroup) {
+          float4 v = fz[q];
+          v.x = __fmul_rn(w0, v.x);  // 0 + w0*s0 == w0*s0 (up to the sign of zero)
+          v.y = __fmul_rn(w0, v.y);  // 0 + w0*s0 == w0*s0 (up to the sign of zero)
+          v.z = __fmul_rn(w0, v.z);  // 0 + w0*s0 == w0*s0 (up to the sign of zero)
+          v.w = __fmul_rn(w0, v.w);  // 0 + w0*s0 == w0*s0 (up to the sign of zero)
+          fz[q] = v;
+          mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+        }
+      } else
+#pragma unroll 1
+      for (int q = j; q < nq; q += kSelGroup) {
+        float4 acc;
+        if (key >= 0) {
+          acc = fz[q];
         } else {
-#pragma unroll
-          for (int i = 0; i < EPT / 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
           for (int k = 0; k < tm.K; ++k) {
             const float wk = tm.w[k];
             if (tm.ptr[k]) {
-              const float* base = sb + tm.slot[k] * CH;
-#pragma unroll
-              for (int i = 0; i < EPT / 4; ++i) {
-                const float4 sv = *reinterpret_cast<const float4*>(base + 4 * (j + kSelGroup * i));
-                acc[i].x = __fadd_rn(acc[i].x, __fmul_rn(wk, sv.x));
-                acc[i].y = __fadd_rn(acc[i].y, __fmul_rn(wk, sv.y));
-                acc[i].z = __fadd_rn(acc[i].z, __fmul_rn(wk, sv.z));
-                acc[i].w = __fadd_rn(acc[i].w, __fmul_rn(wk, sv.w));
-              }
+              const float4 sv = reinterpret_cast<const float4*>(sb + tm.slot[k] * CH)[q];
+              acc.x = __fadd_rn(acc.x, __fmul_rn(wk, sv.x));
+              acc.y = __fadd_rn(acc.y, __fmul_rn(wk, sv.y));
+              acc.z = __fadd_rn(acc.z, __fmul_rn(wk, sv.z));
+              acc.w = __fadd_rn(acc.w, __fmul_rn(wk, sv.w));
             } else {
               const float cv = __fmul_rn(wk, tm.cst[k]);
-#pragma unroll
-              for (int i = 0; i < EPT / 4; ++i) {
-                acc[i].x = __fadd_rn(acc[i].x, cv);
-                acc[i].y = __fadd_rn(acc[i].y, cv);
-                acc[i].z = __fadd_rn(acc[i].z, cv);
-                acc[i].w = __fadd_rn(acc[i].w, cv);
-              }
+              acc.x = __fadd_rn(acc.x, cv);
+              acc.y = __fadd_rn(acc.y, cv);
+              acc.z = __fadd_rn(acc.z, cv);
+              acc.w = __fadd_rn(acc.w, cv);
             }
           }
         }
-#pragma unroll
-        for (int i = 0; i < EPT / 4; ++i) {
-          val[4 * i + 0] = acc[i].x;
-          val[4 * i + 1] = acc[i].y;
-          val[4 * i + 2] = acc[i].z;
-          val[4 * i + 3] = acc[i].w;
+        if (4 * q + 3 >= n_ch) {  // tail of a vocabulary that is not a multiple of 4
+          if (4 * q + 1 >= n_ch) acc.y = -INFINITY;
+          if (4 * q + 2 >= n_ch) acc.z = -INFINITY;
+          acc.w = -INFINITY;
         }
+        if (key < 0) fz[q] = acc;
+        mx = fmaxf(fmaxf(mx, fmaxf(acc.x, acc.y)), fmaxf(acc.z, acc.w));
       }
       // the fused score of eos is needed even when eos is not a pre-beam candidate (:180-181)
-      if (d.key < 0 && d.eos >= e0 && d.eos < e0 + CH) {
-        const int q = (d.eos - e0) >> 2;
-        if (q % kSelGroup == j) {
-          const int ii = 4 * (q / kSelGroup) + (d.eos & 3);
-#pragma unroll
-          for (int i = 0; i < EPT; ++i)
-            if (i == ii) S->w_eos = val[i];
-        }
-      }
-      // elements past the end of the vocabulary never qualify: NaN fails every comparison below
-      if (n_ch < CH) {
-#pragma unroll
-        for (int i = 0; i < EPT; ++i)
-          if (4 * (j + kSelGroup * (i >> 2)) + (i & 3) >= n_ch) val[i] = __int_as_float(0x7fc00000);
-      }
-      float mx = -INFINITY;
-#pragma unroll
-      for (int i = 0; i < EPT; ++i) mx = fmaxf(mx, val[i]);
-      // ---- threshold of the first chunk: at least n_sel elements are >= the k-th largest lane maximum
-      //      of every warp (k = ceil(n_sel / kSelWarps)) ------------------------------------------------
-      if (c == 0) {
-        unsigned cur = (mx > -INFINITY) ? f2ord(mx) : 0u;
+      if (key < 0 && d.eos >= e0 && d.eos < e0 + n_ch && (((d.eos - e0) >> 2) % kSelGroup) == j)
+        S->w_eos = reinterpret_cast<const float*>(fz)[d.eos - e0];
+      unsigned long long thr = tau;
+      if (n_top < n_sel) {
+        // ---- threshold of a chunk met with a non-full list: at least n_sel elements of the chunk are >=
+        //      the kk-th largest lane maximum of every active warp (kk = ceil(n_sel / active warps)) ------
+        const int nw_act = min(kSelWarps, (nq + 31) >> 5);
+        const int kk = (n_sel + nw_act - 1) / nw_act;
+        unsigned co = (mx > -INFINITY) ? f2ord(mx + 0.0f) : 0u;
         unsigned kth = 0u;
-        const int kk = (n_sel + kSelWarps - 1) / kSelWarps;
         for (int r = 0; r < kk; ++r) {
-          kth = __reduce_max_sync(FULLMASK, cur);
-          const unsigned holders = __ballot_sync(FULLMASK, cur == kth);
-          if (lane == __ffs(holders) - 1) cur = 0u;
+          kth = __reduce_max_sync(FULLMASK, co);
+          const unsigned holders = __ballot_sync(FULLMASK, co == kth);
+          if (lane == __ffs(holders) - 1) co = 0u;
         }
         if (lane == 0) S->wkth[wj] = kth;
         group_bar(kBarSel, kSelGroup);
         unsigned mn = S->wkth[0];
-#pragma unroll
-        for (int w2 = 1; w2 < kSelWarps; ++w2) mn = min(mn, S->wkth[w2]);
-        tau_v = (mn == 0u) ? -INFINITY : ord2f(mn);
-        tau_i = 0x7fffffff;
+        for (int w2 = 1; w2 < nw_act; ++w2) mn = min(mn, S->wkth[w2]);
+        const unsigned long long thr_c = (mn == 0u) ? 0ull : (((unsigned long long)mn << 32) | 0x80000000ull);
+        thr = thr_c > thr ? thr_c : thr;
+        if (c == 0) LGASR_TR(1, 3);
       }
-      // ---- push / merge until no element of the chunk is left behind ---------------------------------
-      unsigned pushed = 0u;
-      bool first_round = true;
-      while (true) {
-        // cheap filter first (one compare per thread), the exact (value, index) test only in warps that pass
-        if (__any_sync(FULLMASK, mx >= tau_v)) {
-          unsigned pmask = 0u;
-#pragma unroll
-          for (int i = 0; i < EPT; ++i) {
-            const int e = e0 + 4 * (j + kSelGroup * (i >> 2)) + (i & 3);
-            if (better(val[i], e, tau_v, tau_i)) pmask |= 1u << i;
+      // ---- sweep 2: push everything above the threshold, merge; repeat while the pending list overflows ----
+      for (int round = 0;; ++round) {
+        const int p = it & 1;
+        unsigned long long* kp = S->keys[cur] + n_top;
+        const float thr_v = thr ? key_val(thr) : -INFINITY;
+        const float* fzs = reinterpret_cast<const float*>(fz);
+#pragma unroll 1
+        for (int q0 = wj * 32; q0 < nq; q0 += kSelGroup) {
+          const int q = q0 + lane;
+          bool ok = false;
+          if (q < nq) {
+            const float4 v = fz[q];
+            ok = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) >= thr_v;
           }
-          pmask &= ~pushed;
-          const int ct = __popc(pmask);
-          int inc = ct;
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(FULLMASK, inc, o);
-            if (lane >= o) inc += v;
-          }
-          const int total = __shfl_sync(FULLMASK, inc, 31);
-          if (total > 0) {
-            int base = 0;
-            if (lane == 31) base = atomicAdd(&S->pend_cnt, total);
-            base = __shfl_sync(FULLMASK, base, 31);
-            int slot = base + inc - ct;
-            unsigned long long* kp = S->keys[S->cur_list] + S->n_top;
-#pragma unroll
-            for (int i = 0; i < EPT; ++i) {
-              if ((pmask >> i) & 1u) {
-                if (slot < kPendCap) {
-                  kp[slot] = pack_key(val[i], e0 + 4 * (j + kSelGroup * (i >> 2)) + (i & 3));
-                  pushed |= 1u << i;
-                } else {
-                  S->overflow = 1;
-                }
-                ++slot;
+          if (ok) {  // rare: a lane with a hit pushes on its own (shared atomics, no warp aggregation)
+#pragma unroll 1
+            for (int u = 0; u < 4; ++u) {
+              const int el = 4 * q + u;
+              if (el >= n_ch) break;
+              const unsigned long long ke = pack_key(fzs[el], e0 + el);
+              bool pu = ke > thr;
+              if (round > 0 && pu) {  // an overflow round: skip what the list already holds
+#pragma unroll 1
+                for (int t = 0; t < n_top; ++t) pu = pu && (S->keys[cur][t] != ke);
+              }
+              if (pu) {
+                const int slot = atomicAdd(&S->pend_cnt[p], 1);
+                if (slot < kPendCap)
+                  kp[slot] = ke;
+                else
+                  S->overflow[p] = 1;
               }
             }
           }
         }
-        group_bar(kBarSel, kSelGroup);  // also: every thread has read its stage values
-        if (first_round && tma && j == 0 && c + NST < nchunks) {
+        group_bar(kBarSel, kSelGroup);  // A: pushes done, every thread has read its stage values
+        const int cnt = S->pend_cnt[p];
+        const int ovf = S->overflow[p];
+        if (!ovf && tma && j == 0 && c + NST < nchunks) {
           fence_proxy_async();
           issue_row_chunk(tm, rowoff, c + NST, CH, NST, V, arena, S);
         }
-        first_round = false;
-        const int cnt = S->pend_cnt;
-        const int ovf = S->overflow;
-        if (cnt == 0) {
-          group_bar(kBarSel, kSelGroup);  // nobody may push into the next chunk's list before everyone has read cnt
-          break;
-        }
-        const int cl = S->cur_list;
-        const int n_l = S->n_top;
-        const int n = n_l + (cnt < kPendCap ? cnt : kPendCap);
-        const unsigned long long* ks = S->keys[cl];
-        unsigned long long* kn = S->keys[cl ^ 1];
-        for (int e = j; e < n; e += kSelGroup) {
-          const unsigned long long ke = ks[e];
-          int rank = 0;
+        if (cnt > 0) {
+          const int n = n_top + (cnt < kPendCap ? cnt : kPendCap);
+          const unsigned long long* ks = S->keys[cur];
+          unsigned long long* kn = S->keys[cur ^ 1];
+          const ulonglong2* ks2 = reinterpret_cast<const ulonglong2*>(ks);
+          const int n2 = n >> 1;
+          for (int e = j; e < n; e += kSelGroup) {
+            const unsigned long long ke = ks[e];
+            int rank = 0;
 #pragma unroll 4
-          for (int o = 0; o < n; ++o) rank += (ks[o] > ke) ? 1 : 0;
-          if (rank < n_sel) kn[rank] = ke;
-        }
-        group_bar(kBarSel, kSelGroup);
-        if (j == 0) {
-          const int nt = n < n_sel ? n : n_sel;
-          S->n_top = nt;
-          S->cur_list = cl ^ 1;
-          S->pend_cnt = 0;
-          S->overflow = 0;
-          S->tau = (nt == n_sel) ? kn[n_sel - 1] : 0ull;
-        }
-        group_bar(kBarSel, kSelGroup);
-        {
-          const unsigned long long tk2 = S->tau;
-          if (tk2) {
-            tau_v = key_val(tk2);
-            tau_i = key_idx(tk2);
-          } else {
-            tau_v = -INFINITY;
-            tau_i = 0x7fffffff;
+            for (int o = 0; o < n2; ++o) {
+              const ulonglong2 k2 = ks2[o];
+              rank += (k2.x > ke) ? 1 : 0;
+              rank += (k2.y > ke) ? 1 : 0;
+            }
+            if (n & 1) rank += (ks[n - 1] > ke) ? 1 : 0;
+            if (rank < n_sel) kn[rank] = ke;
+          }
+          group_bar(kBarSel, kSelGroup);  // B: the merged list is complete
+          if (j == 0) {
+            S->pend_cnt[p] = 0;
+            S->overflow[p] = 0;
+          }
+          n_top = n < n_sel ? n : n_sel;
+          cur ^= 1;
+          ++it;
+          if (n_top == n_sel) {
+            tau = S->keys[cur][n_sel - 1];
+            thr = tau > thr ? tau : thr;
           }
         }
         if (!ovf) break;
       }
+      if (c == 0) LGASR_TR(1, 4);
+    }
+    if (j == 0) {
+      S->n_top = n_top;
+      S->cur_list = cur;
     }
     LGASR_TR(1, 2);
     // ---- gather the candidates' posterior rows (first group) by TMA ------------------------------------
-    if (mode == kModePreBeam && wj == 0) {
-      const int nt = S->n_top;
-      issue_cand_rows(d, S->keys[S->cur_list], 0, nt < sl.rows_per_group ? nt : sl.rows_per_group, xT_b, arena, S, lane);
-    }
+    if (mode == kModePreBeam && wj == 0)
+      issue_cand_rows(d, S->keys[cur], 0, n_top < sl.rows_per_group ? n_top : sl.rows_per_group, xT_b, arena, S, lane);
   }
   __syncthreads();
   LGASR_TR(0, 3);
@@ -615,6 +638,9 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     const int RPG = sl.rows_per_group;
     const int nq = Tp >> 2;
     constexpr float kL2E = 1.4426950408889634f;
+    // one candidate per half warp: candidate i of a group belongs to warp i % 8 (the warp whose mbarrier its
+    // row was issued on), half (i / 8) % 2, round i / 16
+    const int half = lane >> 4, hl = lane & 15;
     int grp = 0;
     for (int g0 = 0; g0 < n_top; g0 += RPG, ++grp) {
       const int g1 = (g0 + RPG < n_top) ? g0 + RPG : n_top;
@@ -622,53 +648,51 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         __syncthreads();  // the arena rows of the previous group have been consumed
         if (warp == 0) issue_cand_rows(d, tk, g0, g1, xT_b, arena, S, lane);
       }
-      bool waited = false;
-      for (int jr = g0 + warp; jr < g1; jr += kStepWarps) {
+      mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand[warp]), (uint32_t)(grp & 1));
+      if (grp == 0) LGASR_TR(0, 4);
+      for (int i0 = warp; i0 < g1 - g0; i0 += 2 * kStepWarps) {  // warp-uniform
+        const int i = i0 + half * kStepWarps;
+        const bool have = i < g1 - g0;
+        const int jr = g0 + (have ? i : i0);
         const int c = key_idx(tk[jr]);
-        const float wfull = (d.key < 0) ? key_val(tk[jr]) : fuse_at(tm, rowoff, c);
-        float psi;
-        if (c == d.eos) {
-          psi = psi_eos;
-        } else if (d.eos != d.blank && c == d.blank) {
-          psi = LGASR_LOGZERO;  // :183-185
-        } else {
-          if (!waited) {
-            mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand[warp]), (uint32_t)(grp & 1));
-            waited = true;
-            if (jr == 0) LGASR_TR(0, 4);
-          }
-          // log psi = logsumexp({phi[t-1] + x[t] : start <= t < T} U {r^n[start-1]})  (:163-171), the way
-          // torch.logsumexp does it (max, sum of exp, log).  phi is pre-shifted and LGASR_NEG outside
-          // [start, T), so the sum runs over whole float4 rows.
-          const float4* x4 = reinterpret_cast<const float4*>(arena + (long long)(jr - g0) * Tp);
-          const float4* p4 = reinterpret_cast<const float4*>((c == last) ? bR1 : bR0);
-          const float rn0 = (olen == 0) ? arena[(long long)(jr - g0) * Tp] : LGASR_LOGZERO;
-          float m = rn0;
-          for (int q = lane; q < nq; q += 32) {
-            const float4 xv = x4[q], pv = p4[q];
-            m = fmaxf(fmaxf(fmaxf(m, pv.x + xv.x), fmaxf(pv.y + xv.y, pv.z + xv.z)), pv.w + xv.w);
-          }
-#pragma unroll
-          for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULLMASK, m, o));
-          // (e - m) first: the subtraction is exact near the maximum, where the terms matter
-          float sum = (lane == 0) ? exp2f((rn0 - m) * kL2E) : 0.f;
-          for (int q = lane; q < nq; q += 32) {
-            const float4 xv = x4[q], pv = p4[q];
-            sum += exp2f((pv.x + xv.x - m) * kL2E) + exp2f((pv.y + xv.y - m) * kL2E) +
-                   exp2f((pv.z + xv.z - m) * kL2E) + exp2f((pv.w + xv.w - m) * kL2E);
-          }
-#pragma unroll
-          for (int o = 16; o >= 1; o >>= 1) sum += __shfl_xor_sync(FULLMASK, sum, o);
-          psi = m + logf(sum);
+        const bool special = (c == d.eos) || (d.eos != d.blank && c == d.blank);
+        // log psi = logsumexp({phi[t-1] + x[t] : start <= t < T} U {r^n[start-1]})  (:163-171), the way
+        // torch.logsumexp does it (max, sum of exp, log).  phi is pre-shifted and LGASR_NEG outside
+        // [start, T), so the sum runs over whole float4 rows.  (A special candidate runs the same code on
+        // whatever its arena slot holds and discards the result.)
+        const float4* x4 = reinterpret_cast<const float4*>(arena + (long long)(jr - g0) * Tp);
+        const float4* p4 = reinterpret_cast<const float4*>((c == last) ? bR1 : bR0);
+        const float rn0 = (olen == 0) ? arena[(long long)(jr - g0) * Tp] : LGASR_LOGZERO;
+        float m = rn0;
+#pragma unroll 1
+        for (int q = hl; q < nq; q += 16) {
+          const float4 xa = x4[q], pa = p4[q];
+          m = fmaxf(fmaxf(fmaxf(m, pa.x + xa.x), fmaxf(pa.y + xa.y, pa.z + xa.z)), pa.w + xa.w);
         }
-        if (lane == 0) {
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULLMASK, m, o));
+        // (e - m) first: the subtraction is exact near the maximum, where the terms matter
+        float sum = (hl == 0) ? ex2_approx((rn0 - m) * kL2E) : 0.f;
+#pragma unroll 1
+        for (int q = hl; q < nq; q += 16) {
+          const float4 xa = x4[q], pa = p4[q];
+          sum += ex2_approx((pa.x + xa.x - m) * kL2E) + ex2_approx((pa.y + xa.y - m) * kL2E) +
+                 ex2_approx((pa.z + xa.z - m) * kL2E) + ex2_approx((pa.w + xa.w - m) * kL2E);
+        }
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) sum += __shfl_xor_sync(FULLMASK, sum, o);
+        float psi = m + logf(sum);
+        if (c == d.eos)
+          psi = psi_eos;
+        else if (special)
+          psi = LGASR_LOGZERO;  // :183-185
+        if (have && hl == 0) {
+          const float wfull = (d.key < 0) ? key_val(tk[jr]) : fuse_at(tm, rowoff, c);
           c_total[jr] = __fadd_rn(__fadd_rn(wfull, __fmul_rn(d.w_ctc, __fsub_rn(psi, s_prev))), hyp_score);
           c_tok[jr] = c;
           c_psi[jr] = psi;
         }
       }
-      // a warp that had nothing to wait for in this group still has to consume the barrier phase
-      if (!waited && (g0 + RPG < n_top)) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand[warp]), (uint32_t)(grp & 1));
     }
     if (lane == 0) {
       // unused pre-beam slots (fewer than S tokens in the vocabulary)
@@ -697,18 +721,23 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   }
 
   // ======================= ticket: the last CTA of the utterance runs the selection ==================
+  // CTA barrier, then ONE fence + atomic by thread 0 (the cooperative-groups grid-sync pattern): the
+  // barrier orders every warp's record stores before thread 0's cumulative gpu-scope fence.
   LGASR_TR(0, 5);
-  if (lane == 0) __threadfence();  // only lane 0 of each warp wrote records
   __syncthreads();
   if (tid == 0) {
+    __threadfence();
     const int old = atomicAdd(d.arrive + b, 1);
-    S->last_flag = (old == n_run - 1) ? 1 : 0;
+    const int is_last = (old == n_run - 1) ? 1 : 0;
+    if (is_last) {
+      __threadfence();
+      d.arrive[b] = 0;
+    }
+    S->last_flag = is_last;
   }
   __syncthreads();
   LGASR_TR(0, 6);
   if (!S->last_flag) return;
-  if (tid == 0) d.arrive[b] = 0;
-  __threadfence();
   utt_select(d, tm, b, pp, step, arena);
   LGASR_TR(0, 7);
 }

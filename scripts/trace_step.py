@@ -26,10 +26,10 @@ out = np.zeros(B * W * 32, np.int64)
 _lib.check(eng.lib.lgasr_debug_trace(eng._h, out.ctypes.data_as(_lib._PI64), out.size))
 tr = out.reshape(B * W, 2, 16)
 t0 = tr[:, 0, 0:1]
-names0 = ["start", "ctc_in", "ctc_done", "joined", "cand_in", "records", "ticket", "select_done"]
-names1 = ["start", "row0_in", "sel_done"]
-rel0 = (tr[:, 0, :8] - t0).astype(np.float64)
-rel1 = (tr[:, 1, :3] - t0).astype(np.float64)
+names0 = ["start", "ctc_in", "ctc_done", "joined", "cand_in", "records", "ticket", "select_done", "scan1_done", "scan2_done"]
+names1 = ["start", "row0_in", "sel_done", "thr_done", "chunk0_done"]
+rel0 = (tr[:, 0, :10] - t0).astype(np.float64)
+rel1 = (tr[:, 1, :5] - t0).astype(np.float64)
 for i, n in enumerate(names0):
     v = rel0[:, i][tr[:, 0, i] != 0]
     if len(v):
