@@ -73,6 +73,14 @@ struct lgasr_handle {
   // per-kernel profiling
   int profiling;
   std::vector<cudaEvent_t> prof_ev;  // 3 per step
+  // CUDA graph of the last device-resident replay (the launch-bound loop of lgasr_decode_replay)
+  cudaGraphExec_t rg_exec;
+  std::vector<const float*> rg_ptrs;
+  std::vector<float> rg_cst, rg_w;
+  long long rg_ld;
+  int rg_steps, rg_pp, rg_rp, rg_step0;
+  cudaStream_t rg_stream;  // the legacy default stream cannot be captured: graphs run on this one
+  cudaEvent_t rg_ev[2];
 };
 
 template <typename T>
@@ -170,6 +178,8 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       sl.CH = (budget / (2 * K)) & ~3;
     }
     sl.NST = nst;
+    sl.nchunks = (d.V + sl.CH - 1) / sl.CH;
+    sl.kk_full = (n_sel + kSelWarps - 1) / kSelWarps;
     sl.tma_rows = 0;  // decided per step from the pointers
     long long arena = (long long)nst * K * sl.CH;
     long long cand = (long long)n_sel * d.Tp;
@@ -288,6 +298,12 @@ extern "C" int lgasr_destroy(lgasr_handle* h) {
   if (!h) return LGASR_OK;
   for (void* p : h->allocs) cudaFree(p);
   for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
+  if (h->rg_exec) cudaGraphExecDestroy(h->rg_exec);
+  if (h->rg_stream) {
+    cudaStreamDestroy(h->rg_stream);
+    cudaEventDestroy(h->rg_ev[0]);
+    cudaEventDestroy(h->rg_ev[1]);
+  }
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->d_logp_stage) cudaFree(h->d_logp_stage);
   for (int s = 0; s < 2; ++s) {
@@ -392,7 +408,7 @@ static int fill_terms(lgasr_handle* h, Terms& tm, const float* const* ptr, const
   return LGASR_OK;
 }
 
-static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st) {
+static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl = false) {
   Dev& d = h->d;
   if (h->step >= d.maxlen_cap) return fail(LGASR_ESTATE, "step %d beyond max_len_cap %d", h->step, d.maxlen_cap);
   dim3 grid(d.W, d.B);
@@ -411,10 +427,22 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st) {
     for (int k = 0; k < tm.K; ++k)
       if (tm.ptr[k]) al = al && ((reinterpret_cast<uintptr_t>(tm.ptr[k]) & 15) == 0);
     sl.tma_rows = al ? 1 : 0;
+    // programmatic dependent launch (only between consecutive k_step launches of a replay, where the
+    // matrices are inputs that no earlier kernel of the stream writes): see the prologue of k_step
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kStepThreads);
+    cfg.dynamicSmemBytes = h->smem_step;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
     if (d.trace)
-      k_step<true><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
+      CK(cudaLaunchKernelEx(&cfg, k_step<true>, d, tm, sl, h->pp, h->rp, h->step));
     else
-      k_step<false><<<grid, kStepThreads, h->smem_step, st>>>(d, tm, sl, h->pp, h->rp, h->step);
+      CK(cudaLaunchKernelEx(&cfg, k_step<false>, d, tm, sl, h->pp, h->rp, h->step));
     LAUNCH_CK();
     if (h->profiling) {
       CK(cudaEventRecord(pe[1], st));
@@ -605,11 +633,85 @@ extern "C" int lgasr_decode_replay(lgasr_handle* h, int n_steps, const float* co
   if (!h) return fail(LGASR_EINVAL, "null handle");
   if (!h->begun) return fail(LGASR_ESTATE, "replay before begin");
   const int K = h->d.K;
-  for (int i = 0; i < n_steps; ++i) {
-    Terms tm;
-    TRY(fill_terms(h, tm, h_term_ptr ? h_term_ptr + (size_t)i * K : nullptr, h_term_const, h_term_weight, ld));
-    TRY(step_impl(h, tm, (cudaStream_t)stream));
+  cudaStream_t user_st = (cudaStream_t)stream;
+  cudaStream_t st = user_st;
+  const char* npdl = getenv("LGASR_NO_PDL");
+  const bool pdl = !h->profiling && !(npdl && npdl[0] == '1');
+  auto run_steps = [&]() -> int {
+    for (int i = 0; i < n_steps; ++i) {
+      Terms tm;
+      TRY(fill_terms(h, tm, h_term_ptr ? h_term_ptr + (size_t)i * K : nullptr, h_term_const, h_term_weight, ld));
+      TRY(step_impl(h, tm, st, pdl && i > 0));
+    }
+    return LGASR_OK;
+  };
+  const char* ng = getenv("LGASR_NO_GRAPH");
+  if (h->profiling || n_steps < 2 || !h_term_ptr || (ng && ng[0] == '1')) return run_steps();
+  if (!h->rg_stream) {
+    CK(cudaStreamCreateWithFlags(&h->rg_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->rg_ev[0], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->rg_ev[1], cudaEventDisableTiming));
   }
+  st = h->rg_stream;
+  // one launch per position and nothing on the host between them: the loop is launch-bound, so it is
+  // captured once into a CUDA graph and replayed while the same buffers are decoded again
+  std::vector<const float*> ptrs(h_term_ptr, h_term_ptr + (size_t)n_steps * K);
+  std::vector<float> cst(K), w(K);
+  for (int k = 0; k < K; ++k) {
+    cst[k] = h_term_const ? h_term_const[k] : 0.f;
+    w[k] = h_term_weight ? h_term_weight[k] : 0.f;
+  }
+  const bool hit = h->rg_exec && h->rg_steps == n_steps && h->rg_ld == (long long)ld && h->rg_pp == h->pp &&
+                   h->rg_rp == h->rp && h->rg_step0 == h->step && h->rg_ptrs == ptrs && h->rg_cst == cst && h->rg_w == w;
+  if (!hit) {
+    if (h->step + n_steps > h->d.maxlen_cap) return fail(LGASR_ESTATE, "replay beyond max_len_cap");
+    if (h->rg_exec) {
+      cudaGraphExecDestroy(h->rg_exec);
+      h->rg_exec = nullptr;
+    }
+    const int pp0 = h->pp, rp0 = h->rp, step0 = h->step;
+    cudaGraph_t g = nullptr;
+    CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const int rc = run_steps();
+    g_launches.fetch_sub(n_steps, std::memory_order_relaxed);  // captured, not launched
+    const cudaError_t ee = cudaStreamEndCapture(st, &g);
+    h->pp = pp0;
+    h->rp = rp0;
+    h->step = step0;
+    if (rc) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    if (ee != cudaSuccess) return fail(LGASR_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ee));
+    const cudaError_t ei = cudaGraphInstantiate(&h->rg_exec, g, 0);
+    cudaGraphDestroy(g);
+    if (ei != cudaSuccess) {
+      h->rg_exec = nullptr;
+      return fail(LGASR_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ei));
+    }
+    h->rg_ptrs.swap(ptrs);
+    h->rg_cst = cst;
+    h->rg_w = w;
+    h->rg_ld = ld;
+    h->rg_steps = n_steps;
+    h->rg_pp = pp0;
+    h->rg_rp = rp0;
+    h->rg_step0 = step0;
+  } else if (h->step + n_steps > h->d.maxlen_cap) {
+    return fail(LGASR_ESTATE, "replay beyond max_len_cap");
+  }
+  CK(cudaEventRecord(h->rg_ev[0], user_st));
+  CK(cudaStreamWaitEvent(st, h->rg_ev[0], 0));
+  CK(cudaGraphLaunch(h->rg_exec, st));
+  CK(cudaEventRecord(h->rg_ev[1], st));
+  CK(cudaStreamWaitEvent(user_st, h->rg_ev[1], 0));
+  g_launches.fetch_add(n_steps, std::memory_order_relaxed);
+  if (n_steps & 1) {
+    h->pp ^= 1;
+    h->rp ^= 1;
+  }
+  h->step += n_steps;
+  h->cache_valid = false;
   return LGASR_OK;
 }
 

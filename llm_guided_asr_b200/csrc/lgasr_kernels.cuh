@@ -359,9 +359,9 @@ __host__ __device__ inline long long utt_select_smem_floats(int W, int R, int NS
   return (long long)W * R * 3 + 2LL * W + (long long)W * (3 + NS) + 2LL * W + 3LL * kSelListCap + 8;
 }
 
-__device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b, int pp, int step, float* smem) {
+__device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b, int pp, int step, float* smem, int n_run,
+                                           int cur_len, long long* tr = nullptr) {
   const int tid = threadIdx.x, nthr = blockDim.x;
-  const int n_run = d.n_run[pp][b];
   const int R = d.R, W = d.W, NS = d.NS;
   const int n_rec_row = (d.mode == kModePreBeam) ? d.S + 1 : d.W;
   const int nrec = n_run * n_rec_row;
@@ -377,19 +377,46 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
   // 8-byte aligned tail: W*R*3 + 2W + 3W + W*NS floats precede it; pad to an even count
   float* tail = p_scores + W * NS;
   if ((tail - smem) & 1) ++tail;
-  unsigned long long* rowmax = reinterpret_cast<unsigned long long*>(tail);  // [W]
-  unsigned long long* c_key = rowmax + W;                                    // [kSelListCap]
+  unsigned* rowmax = reinterpret_cast<unsigned*>(tail);  // [W] best ordered total of each row (upper key halves); 2W floats reserved
+  unsigned long long* c_key = reinterpret_cast<unsigned long long*>(tail) + W;  // [kSelListCap]
   int* c_e = reinterpret_cast<int*>(c_key + kSelListCap);                    // [kSelListCap]
   int* sh_nsel = c_e + kSelListCap;
   int* sh_cnt = sh_nsel + 1;
-  const int cur_len = d.cur_len[pp][b];
   const int maxlen = d.maxlen[b], minlen = d.minlen[b];
   const bool last = (step == maxlen - 1);
   const int new_len = cur_len + 1 + (last ? 1 : 0);
   float* bbl = d.best_by_len + (long long)b * (d.Lcap + 2);
-  // scalars of the serial part (only this utterance's selection ever writes them)
   int n_end0 = 0;
   float best_all0 = 0.f, bbl_new0 = 0.f, bbl_m[3] = {-INFINITY, -INFINITY, -INFINITY};
+  // row-maximum prefilter: with W running rows, the W row maxima are W distinct records, so nothing below
+  // their minimum can be among the W best; typically ~2W of the W*(S+1) records survive
+  const bool prefilter = (n_run >= W) && (nrec <= 2 * nthr);
+  if (tid < W) rowmax[tid] = 0u;
+  if (tid == 0) *sh_cnt = 0;
+  if (prefilter) __syncthreads();
+  // first pass of both loops: every global load is issued before anything is consumed (one round trip)
+  const int npar = n_run * (3 + NS);
+  int tok0 = -1, h0 = 0;
+  float tot0 = 0.f, psi0 = 0.f;
+  if (tid < nrec) {
+    h0 = tid / n_rec_row;
+    const long long o = (long long)(b * W + h0) * R + (tid - h0 * n_rec_row);
+    tok0 = __ldcg(d.cand_tok + o);  // written by other CTAs of this launch: read through L2
+    tot0 = __ldcg(d.cand_total + o);
+    psi0 = __ldcg(d.cand_psi + o);
+  }
+  unsigned pv0 = 0u;
+  int ph0 = 0, pf0 = 0;
+  if (tid < npar) {
+    ph0 = tid / (3 + NS);
+    pf0 = tid - ph0 * (3 + NS);
+    const int prow = b * W + ph0;
+    if (pf0 == 0) pv0 = (unsigned)d.run_slot[pp][prow];
+    else if (pf0 == 1) pv0 = (unsigned)d.rmeta[pp][prow].y;
+    else if (pf0 == 2) pv0 = __float_as_uint(d.s_prev[pp][prow]);
+    else pv0 = __float_as_uint(d.scores[pp][(long long)prow * NS + (pf0 - 3)]);
+  }
+  // scalars of the serial part (only this utterance's selection ever writes them)
   if (tid == 0) {
     n_end0 = d.n_ended[b];
     best_all0 = d.best_all[b];
@@ -400,44 +427,47 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
       if (len >= 0 && len <= d.Lcap + 1) bbl_m[m] = bbl[len];
     }
   }
-  // row-maximum prefilter: with W running rows, the W row maxima are W distinct records, so nothing below
-  // their minimum can be among the W best; typically ~2W of the W*(S+1) records survive
-  const bool prefilter = (n_run >= W) && (nrec <= 2 * nthr);
-  if (tid < W) rowmax[tid] = 0ull;
-  if (tid == 0) *sh_cnt = 0;
-  if (prefilter) __syncthreads();
-  for (int e = tid; e < nrec; e += nthr) {
-    const int h = e / n_rec_row, j = e - h * n_rec_row;
-    const long long o = (long long)(b * W + h) * R + j;
-    const int tok = __ldcg(d.cand_tok + o);  // written by other CTAs of this launch: read through L2
-    const float tot = __ldcg(d.cand_total + o);
-    r_psi[e] = __ldcg(d.cand_psi + o);
+  auto put_record = [&](int e, int h, int tok, float tot, float psi) {
+    r_psi[e] = psi;
     unsigned u = __float_as_uint(tot + 0.0f);
     u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
     const unsigned long long ke = tok >= 0 ? (((unsigned long long)u << 32) | (unsigned)(~(h * d.V + tok))) : 0ull;
     r_key[e] = ke;
-    if (prefilter && ke) atomicMax(rowmax + h, ke);
+    if (prefilter && ke) atomicMax(rowmax + h, (unsigned)(ke >> 32));  // native 32-bit shared atomic
+  };
+  auto put_parent = [&](int h, int f, unsigned v) {
+    if (f == 0) p_slot[h] = (int)v;
+    else if (f == 1) p_last[h] = (int)v;
+    else if (f == 2) p_sprev[h] = __uint_as_float(v);
+    else p_scores[h * NS + (f - 3)] = __uint_as_float(v);
+  };
+  if (tid < nrec) put_record(tid, h0, tok0, tot0, psi0);
+  if (tid < npar) put_parent(ph0, pf0, pv0);
+  for (int e = tid + nthr; e < nrec; e += nthr) {  // wide beams only
+    const int h = e / n_rec_row, j = e - h * n_rec_row;
+    const long long o = (long long)(b * W + h) * R + j;
+    put_record(e, h, __ldcg(d.cand_tok + o), __ldcg(d.cand_total + o), __ldcg(d.cand_psi + o));
   }
-  for (int i = tid; i < n_run * (3 + NS); i += nthr) {
+  for (int i = tid + nthr; i < npar; i += nthr) {
     const int h = i / (3 + NS), f = i - h * (3 + NS);
     const int prow = b * W + h;
-    if (f == 0) p_slot[h] = d.run_slot[pp][prow];
-    else if (f == 1) p_last[h] = d.rmeta[pp][prow].y;
-    else if (f == 2) p_sprev[h] = d.s_prev[pp][prow];
-    else p_scores[h * NS + (f - 3)] = d.scores[pp][(long long)prow * NS + (f - 3)];
+    unsigned v;
+    if (f == 0) v = (unsigned)d.run_slot[pp][prow];
+    else if (f == 1) v = (unsigned)d.rmeta[pp][prow].y;
+    else if (f == 2) v = __float_as_uint(d.s_prev[pp][prow]);
+    else v = __float_as_uint(d.scores[pp][(long long)prow * NS + (f - 3)]);
+    put_parent(h, f, v);
   }
   if (tid < W) sel[tid] = -1;
   __syncthreads();
+  if (tr && tid == 0) tr[9 + 3] = clock64();
   bool ranked = false;
   if (prefilter) {
-    unsigned long long tau = ~0ull;
-    for (int h = 0; h < W; ++h) {
-      const unsigned long long rmx = rowmax[h];
-      tau = rmx < tau ? rmx : tau;
-    }
+    unsigned tau = 0xffffffffu;  // minimum over the rows of the best ordered total
+    for (int h = 0; h < W; ++h) tau = min(tau, rowmax[h]);
     for (int e = tid; e < nrec; e += nthr) {
       const unsigned long long ke = r_key[e];
-      if (ke != 0ull && ke >= tau) {
+      if (ke != 0ull && (unsigned)(ke >> 32) >= tau) {
         const int slot = atomicAdd(sh_cnt, 1);
         if (slot < kSelListCap) {
           c_key[slot] = ke;
@@ -523,54 +553,72 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
     }
   }
 
-  if (tid == 0) {
-    int nsel = 0;
-    while (nsel < W && sel[nsel] >= 0) ++nsel;
-    int nrun_new = 0;
-    int n_end = n_end0;
-    float best_all = best_all0;
+  if (tr && tid == 0) tr[10] = clock64();
+  // bookkeeping by warp 0, 32 ranks at a time: where each kept record goes (running slot / ended pool /
+  // dropped), in rank order exactly like the reference's loop over the best list (:325-362, :400-429)
+  if (tid < 32) {
+    const int lane = tid;
+    const unsigned lt = (1u << lane) - 1u;
+    int nsel = 0, nrun_new = 0, n_end = __shfl_sync(FULLMASK, n_end0, 0);
     float best_new = -INFINITY;  // best ended score of this step: all of them have length new_len
-    for (int j = 0; j < nsel; ++j) {
-      const int e = sel[j];
-      const int tok = (int)(~(unsigned)r_key[e]) % d.V;
-      const bool is_eos = last || tok == d.eos;
+    for (int base = 0; base < W; base += 32) {
+      const int j = base + lane;
+      const int e = (j < W) ? sel[j] : -1;
+      const bool valid = e >= 0;
+      int tok = -1;
+      if (valid) tok = (int)(~(unsigned)r_key[e]) - (e / n_rec_row) * d.V;
+      const bool is_eos = valid && (last || tok == d.eos);
+      const bool elig = is_eos && step >= minlen;
+      const bool run = valid && !is_eos;
+      const unsigned m_valid = __ballot_sync(FULLMASK, valid);
+      const unsigned m_el = __ballot_sync(FULLMASK, elig);
+      const unsigned m_run = __ballot_sync(FULLMASK, run);
+      float sc = -INFINITY;
+      if (run) dest[j] = nrun_new + __popc(m_run & lt);
       if (is_eos) {
-        if (step >= minlen && n_end < d.Ecap) {
-          dest[j] = -1 - n_end;
-          const float sc = key_total(r_key[e]);
-          d.end_score[(long long)b * d.Ecap + n_end] = sc;
-          d.end_meta[(long long)b * d.Ecap + n_end] = make_int4(step, j, new_len, last ? 1 : 0);
-          if (sc > best_new) best_new = sc;
-          ++n_end;
+        const int my_end = n_end + __popc(m_el & lt);
+        if (elig && my_end < d.Ecap) {
+          dest[j] = -1 - my_end;
+          sc = key_total(r_key[e]);
+          d.end_score[(long long)b * d.Ecap + my_end] = sc;
+          d.end_meta[(long long)b * d.Ecap + my_end] = make_int4(step, j, new_len, last ? 1 : 0);
         } else {
           dest[j] = INT_MIN;
         }
-      } else {
-        dest[j] = nrun_new++;
       }
-    }
-    if (best_new > -INFINITY) {
-      if (best_new > best_all) best_all = best_new;
-      if (best_new > bbl_new0) bbl[new_len] = best_new;
-      d.n_ended[b] = n_end;
-      d.best_all[b] = best_all;
-    }
-    // end detection (e2e_asr_common.py:17-48): lengths step, step-1, step-2 (none of them is new_len)
-    bool fin = (nrun_new == 0) || last;
-    if (!fin && d.end_detect && n_end > 0) {
-      int count = 0;
 #pragma unroll
-      for (int m = 0; m < 3; ++m) {
-        const float bs = bbl_m[m];
-        if (bs > -INFINITY && ((double)bs - (double)best_all) < d.d_end) ++count;
-      }
-      if (count == 3) fin = true;
+      for (int o = 16; o >= 1; o >>= 1) sc = fmaxf(sc, __shfl_xor_sync(FULLMASK, sc, o));
+      best_new = fmaxf(best_new, sc);
+      n_end = min(n_end + __popc(m_el), d.Ecap);
+      nrun_new += __popc(m_run);
+      nsel += __popc(m_valid);
     }
-    d.n_run[pp ^ 1][b] = nrun_new;
-    d.cur_len[pp ^ 1][b] = cur_len + 1;
-    d.done[pp ^ 1][b] = fin ? 1 : 0;
-    *sh_nsel = nsel;
+    if (lane == 0) {
+      float best_all = best_all0;
+      if (best_new > -INFINITY) {
+        if (best_new > best_all) best_all = best_new;
+        if (best_new > bbl_new0) bbl[new_len] = best_new;
+        d.n_ended[b] = n_end;
+        d.best_all[b] = best_all;
+      }
+      // end detection (e2e_asr_common.py:17-48): lengths step, step-1, step-2 (none of them is new_len)
+      bool fin = (nrun_new == 0) || last;
+      if (!fin && d.end_detect && n_end > 0) {
+        int count = 0;
+#pragma unroll
+        for (int m = 0; m < 3; ++m) {
+          const float bs = bbl_m[m];
+          if (bs > -INFINITY && ((double)bs - (double)best_all) < d.d_end) ++count;
+        }
+        if (count == 3) fin = true;
+      }
+      d.n_run[pp ^ 1][b] = nrun_new;
+      d.cur_len[pp ^ 1][b] = cur_len + 1;
+      d.done[pp ^ 1][b] = fin ? 1 : 0;
+      *sh_nsel = nsel;
+    }
   }
+  if (tr && tid == 0) tr[11] = clock64();
   __syncthreads();
   const int nsel = *sh_nsel;
   // per-hypothesis fields
@@ -639,7 +687,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
     if (threadIdx.x == 0) utt_carry_done(d, b, pp);
     return;
   }
-  utt_select(d, tm, b, pp, step, smem);
+  utt_select(d, tm, b, pp, step, smem, d.n_run[pp][b], d.cur_len[pp][b]);
 }
 
 // ------------------------------------------------------------------------------------------

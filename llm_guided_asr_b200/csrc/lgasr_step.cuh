@@ -32,7 +32,9 @@ constexpr int kStepWarps = kStepThreads / 32;
 
 struct StepLaunch {
   int CH;              // floats per chunk per term (multiple of 4)
-  int NST;             // stages in flight
+  int NST;             // stages in flight (1 or 2)
+  int nchunks;         // ceil(V / CH)
+  int kk_full;         // ceil(n_sel / kSelWarps): lane-maximum rounds of the chunk threshold
   int tma_rows;        // 1: full-scorer rows are 16-byte aligned -> bulk copies; 0: plain loads
   int arena_floats;    // union buffer: row stages | candidate rows | selection scratch
   int rows_per_group;  // candidate rows that fit the arena
@@ -256,6 +258,16 @@ struct __align__(16) StepSmem {
       d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2 + (grp)) * 16 + (i)] = clock64(); \
   } while (0)
 
+__device__ __forceinline__ long long gtimer() {
+  long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define LGASR_GT(i)                                                                                     \
+  do {                                                                                                  \
+    if (TR && tid == 0) d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 + (i)] = gtimer(); \
+  } while (0)
+
 constexpr int kBarCtc = 1, kBarSel = 2;  // named barriers of the two groups (0 = __syncthreads)
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -267,7 +279,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 // issue the TMA copies of chunk c of this hypothesis' full-scorer rows into its stage
 __device__ __forceinline__ void issue_row_chunk(const Terms& tm, long long rowoff, int c, int CH, int NST, int V, float* arena,
                                                 StepSmem* S) {
-  const int stage = c % NST;
+  const int stage = c & (NST - 1);
   const int n = min(CH, V - c * CH);
   const uint32_t bytes = (uint32_t)n * 4u;
   unsigned long long* bar = &S->bar_full[stage];
@@ -334,17 +346,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   const int tid = threadIdx.x;
   const int W = d.W, V = d.V, Tp = d.Tp;
   const int row = b * W + h;
-  // per-hypothesis metadata: one batch of independent loads (rows h >= n_run hold stale but valid memory)
-  const int done = d.done[pp][b], n_run = d.n_run[pp][b];
-  const int T = d.xlen[b];
-  const int cur_len = d.cur_len[pp][b];
-  const int4 rm = d.rmeta[pp][row];  // parent slot, last token, parent's last token
-  const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
-  const float hyp_score = d.score[pp][row];
-  if (done || h >= n_run) {
-    if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
-    return;
-  }
+  const long long rowoff = (long long)row * tm.ld;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   StepSmem* S = reinterpret_cast<StepSmem*>(smem_raw);
   float* bR0 = reinterpret_cast<float*>(smem_raw + sizeof(StepSmem));
@@ -355,15 +357,53 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   float* bD = bC + Tp;
   float* arena = bD + Tp;
   const int CH = sl.CH, NST = sl.NST;
-  const int nchunks = (V + CH - 1) / CH;
+  const int nchunks = sl.nchunks;
   const bool tma = sl.tma_rows != 0;
+  const int mode = d.mode;
+  // ---- programmatic dependent launch: everything up to griddepcontrol.wait touches only kernel parameters,
+  // this CTA's shared memory and the full-scorer matrices (inputs of the step, never written by the previous
+  // k_step), so under PDL it overlaps the previous position's selection tail: the next grid's CTAs take the
+  // slots of CTAs that have left and have their score rows in flight before the previous grid has drained.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (tid == kCtcThreads) {
+#pragma unroll
+    for (int i = 0; i < kMaxStages; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_full[i]), 1);
+#pragma unroll
+    for (int i = 0; i < kStepWarps; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_cand[i]), 1);
+    S->pend_cnt[0] = S->pend_cnt[1] = 0;
+    S->overflow[0] = S->overflow[1] = 0;
+    S->n_top = 0;
+    S->cur_list = 0;
+    S->w_eos = 0.f;
+    S->psi_eos = 0.f;
+    mbar_fence_init();
+    if (tma && mode != kModeFullCtc) {
+      const int pre = nchunks < NST ? nchunks : NST;
+      for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
+    }
+  }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // per-hypothesis metadata: one batch of independent loads (rows h >= n_run hold stale but valid memory)
+  const int done = d.done[pp][b], n_run = d.n_run[pp][b];
+  const int T = d.xlen[b];
+  const int cur_len = d.cur_len[pp][b];
+  const int4 rm = d.rmeta[pp][row];  // parent slot, last token, parent's last token
+  const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
+  const float hyp_score = d.score[pp][row];
+  if (done || h >= n_run) {
+    if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
+    // the row copies already in flight target this CTA's shared memory: let them land before leaving
+    if (tid == kCtcThreads && tma && mode != kModeFullCtc) {
+      const int pre = nchunks < NST ? nchunks : NST;
+      for (int c = 0; c < pre; ++c) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[c]), 0);
+    }
+    return;
+  }
 
   const int lane = tid & 31, warp = tid >> 5;
-  const long long rowoff = (long long)row * tm.ld;
   const int olen = cur_len - 1;
   const int last = rm.y;
   const float* xT_b = d.xT + (long long)b * V * Tp;
-  const int mode = d.mode;
   const int n_sel = (mode == kModePreBeam) ? d.S : d.W;
   const int has_parent = rm.x >= 0;
 
@@ -381,26 +421,11 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         bulk_g2s(bC, xT_b + (long long)d.blank * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
       }
     }
-  } else if (tid == kCtcThreads) {
-#pragma unroll
-    for (int i = 0; i < kMaxStages; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_full[i]), 1);
-#pragma unroll
-    for (int i = 0; i < kStepWarps; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_cand[i]), 1);
-    S->pend_cnt[0] = S->pend_cnt[1] = 0;
-    S->overflow[0] = S->overflow[1] = 0;
-    S->n_top = 0;
-    S->cur_list = 0;
-    S->w_eos = 0.f;
-    S->psi_eos = 0.f;
-    mbar_fence_init();
-    if (tma && mode != kModeFullCtc) {
-      const int pre = nchunks < NST ? nchunks : NST;
-      for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
-    }
   }
   __syncthreads();
   LGASR_TR(0, 0);
   LGASR_TR(1, 0);
+  LGASR_GT(14);
 
   if (tid < kCtcThreads) {
     // ======================= ctc group: CTC state of this hypothesis ==================================
@@ -425,13 +450,13 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     int cur = 0, n_top = 0, it = 0;
     unsigned long long tau = 0ull;  // key of the n_sel-th best so far (0 = list not full)
     for (int c = 0; c < nchunks; ++c) {
-      const int stage = tma ? c % NST : 0;
+      const int stage = tma ? (c & (NST - 1)) : 0;  // NST is 1 or 2
       const int e0 = c * CH;
       const int n_ch = min(CH, V - e0);
       const int nq = (n_ch + 3) >> 2;
       float* sb = arena + (long long)stage * srows * CH;
       if (tma) {
-        mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[stage]), (uint32_t)((c / NST) & 1));
+        mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[stage]), (uint32_t)((c >> (NST - 1)) & 1));
       } else {
         // rows that are not 16-byte aligned: the group stages the chunk with plain loads
 #pragma unroll 1
@@ -505,7 +530,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         // ---- threshold of a chunk met with a non-full list: at least n_sel elements of the chunk are >=
         //      the kk-th largest lane maximum of every active warp (kk = ceil(n_sel / active warps)) ------
         const int nw_act = min(kSelWarps, (nq + 31) >> 5);
-        const int kk = (n_sel + nw_act - 1) / nw_act;
+        const int kk = (nw_act == kSelWarps) ? sl.kk_full : (n_sel + nw_act - 1) / nw_act;
         unsigned co = (mx > -INFINITY) ? f2ord(mx + 0.0f) : 0u;
         unsigned kth = 0u;
         for (int r = 0; r < kk; ++r) {
@@ -513,10 +538,11 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           const unsigned holders = __ballot_sync(FULLMASK, co == kth);
           if (lane == __ffs(holders) - 1) co = 0u;
         }
-        if (lane == 0) S->wkth[wj] = kth;
+        if (lane == 0) S->wkth[wj] = (wj < nw_act) ? kth : 0xffffffffu;  // idle warps do not vote
         group_bar(kBarSel, kSelGroup);
         unsigned mn = S->wkth[0];
-        for (int w2 = 1; w2 < nw_act; ++w2) mn = min(mn, S->wkth[w2]);
+#pragma unroll
+        for (int w2 = 1; w2 < kSelWarps; ++w2) mn = min(mn, S->wkth[w2]);
         const unsigned long long thr_c = (mn == 0u) ? 0ull : (((unsigned long long)mn << 32) | 0x80000000ull);
         thr = thr_c > thr ? thr_c : thr;
         if (c == 0) LGASR_TR(1, 3);
@@ -526,34 +552,32 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         const int p = it & 1;
         unsigned long long* kp = S->keys[cur] + n_top;
         const float thr_v = thr ? key_val(thr) : -INFINITY;
-        const float* fzs = reinterpret_cast<const float*>(fz);
+        // rare path: a lane with a hit pushes on its own (shared atomics, no warp aggregation)
+        auto push = [&](float val, int el) {
+          if (val >= thr_v && el < n_ch) {
+            const unsigned long long ke = pack_key(val, e0 + el);
+            bool pu = ke > thr;
+            if (round > 0 && pu) {  // an overflow round: skip what the list already holds
 #pragma unroll 1
-        for (int q0 = wj * 32; q0 < nq; q0 += kSelGroup) {
-          const int q = q0 + lane;
-          bool ok = false;
-          if (q < nq) {
-            const float4 v = fz[q];
-            ok = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) >= thr_v;
-          }
-          if (ok) {  // rare: a lane with a hit pushes on its own (shared atomics, no warp aggregation)
-#pragma unroll 1
-            for (int u = 0; u < 4; ++u) {
-              const int el = 4 * q + u;
-              if (el >= n_ch) break;
-              const unsigned long long ke = pack_key(fzs[el], e0 + el);
-              bool pu = ke > thr;
-              if (round > 0 && pu) {  // an overflow round: skip what the list already holds
-#pragma unroll 1
-                for (int t = 0; t < n_top; ++t) pu = pu && (S->keys[cur][t] != ke);
-              }
-              if (pu) {
-                const int slot = atomicAdd(&S->pend_cnt[p], 1);
-                if (slot < kPendCap)
-                  kp[slot] = ke;
-                else
-                  S->overflow[p] = 1;
-              }
+              for (int t = 0; t < n_top; ++t) pu = pu && (S->keys[cur][t] != ke);
             }
+            if (pu) {
+              const int slot = atomicAdd(&S->pend_cnt[p], 1);
+              if (slot < kPendCap)
+                kp[slot] = ke;
+              else
+                S->overflow[p] = 1;
+            }
+          }
+        };
+#pragma unroll 1
+        for (int q = j; q < nq; q += kSelGroup) {
+          const float4 v = fz[q];
+          if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) >= thr_v) {
+            push(v.x, 4 * q);
+            push(v.y, 4 * q + 1);
+            push(v.z, 4 * q + 2);
+            push(v.w, 4 * q + 3);
           }
         }
         group_bar(kBarSel, kSelGroup);  // A: pushes done, every thread has read its stage values
@@ -737,9 +761,11 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   }
   __syncthreads();
   LGASR_TR(0, 6);
+  LGASR_GT(15);
   if (!S->last_flag) return;
-  utt_select(d, tm, b, pp, step, arena);
+  utt_select(d, tm, b, pp, step, arena, n_run, cur_len, TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
   LGASR_TR(0, 7);
+  LGASR_GT(15);
 }
 
 }  // namespace lgasr

@@ -26,9 +26,9 @@ out = np.zeros(B * W * 32, np.int64)
 _lib.check(eng.lib.lgasr_debug_trace(eng._h, out.ctypes.data_as(_lib._PI64), out.size))
 tr = out.reshape(B * W, 2, 16)
 t0 = tr[:, 0, 0:1]
-names0 = ["start", "ctc_in", "ctc_done", "joined", "cand_in", "records", "ticket", "select_done", "scan1_done", "scan2_done"]
+names0 = ["start", "ctc_in", "ctc_done", "joined", "cand_in", "records", "ticket", "select_done", "scan1_done", "scan2_done", "sel_ranked", "sel_booked", "sel_loaded"]
 names1 = ["start", "row0_in", "sel_done", "thr_done", "chunk0_done"]
-rel0 = (tr[:, 0, :10] - t0).astype(np.float64)
+rel0 = (tr[:, 0, :13] - t0).astype(np.float64)
 rel1 = (tr[:, 1, :5] - t0).astype(np.float64)
 for i, n in enumerate(names0):
     v = rel0[:, i][tr[:, 0, i] != 0]
@@ -38,3 +38,11 @@ for i, n in enumerate(names1):
     v = rel1[:, i][tr[:, 1, i] != 0]
     if len(v):
         print(f"sel     {n:12s} n={len(v):4d} median={np.median(v):9.0f} p90={np.percentile(v, 90):9.0f} max={v.max():9.0f} cycles")
+
+last = tr[:, 0, 7] > tr[:, 0, 6]
+d = lambda a, b_: np.median((tr[last, 0, a] - tr[last, 0, b_]).astype(np.float64))
+print(f"select CTAs: n={last.sum()} ticket->loaded {d(12, 6):.0f}  loaded->ranked {d(10, 12):.0f}  ranked->booked {d(11, 10):.0f}  booked->done {d(7, 11):.0f}  total {d(7, 6):.0f}")
+
+g0, g1 = tr[:, 0, 14], tr[:, 0, 15]
+print(f"globaltimer: CTA starts spread {(g0.max() - g0.min()) / 1e3:.2f} us; first start -> last end {(g1.max() - g0.min()) / 1e3:.2f} us; "
+      f"median CTA life {np.median(g1 - g0) / 1e3:.2f} us; last ticket-CTA end - first start: {(g1[~last].max() - g0.min()) / 1e3:.2f} us")
