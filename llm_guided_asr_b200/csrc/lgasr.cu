@@ -439,6 +439,7 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
+    sl.pdl = pdl ? 1 : 0;
     if (d.trace)
       CK(cudaLaunchKernelEx(&cfg, k_step<true>, d, tm, sl, h->pp, h->rp, h->step));
     else

@@ -360,7 +360,7 @@ __host__ __device__ inline long long utt_select_smem_floats(int W, int R, int NS
 }
 
 __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b, int pp, int step, float* smem, int n_run,
-                                           int cur_len, long long* tr = nullptr) {
+                                           int cur_len, int maxlen, int minlen, long long* tr = nullptr) {
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int R = d.R, W = d.W, NS = d.NS;
   const int n_rec_row = (d.mode == kModePreBeam) ? d.S + 1 : d.W;
@@ -382,7 +382,6 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
   int* c_e = reinterpret_cast<int*>(c_key + kSelListCap);                    // [kSelListCap]
   int* sh_nsel = c_e + kSelListCap;
   int* sh_cnt = sh_nsel + 1;
-  const int maxlen = d.maxlen[b], minlen = d.minlen[b];
   const bool last = (step == maxlen - 1);
   const int new_len = cur_len + 1 + (last ? 1 : 0);
   float* bbl = d.best_by_len + (long long)b * (d.Lcap + 2);
@@ -687,7 +686,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
     if (threadIdx.x == 0) utt_carry_done(d, b, pp);
     return;
   }
-  utt_select(d, tm, b, pp, step, smem, d.n_run[pp][b], d.cur_len[pp][b]);
+  utt_select(d, tm, b, pp, step, smem, d.n_run[pp][b], d.cur_len[pp][b], d.maxlen[b], d.minlen[b]);
 }
 
 // ------------------------------------------------------------------------------------------

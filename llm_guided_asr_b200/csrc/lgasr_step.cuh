@@ -35,6 +35,7 @@ struct StepLaunch {
   int NST;             // stages in flight (1 or 2)
   int nchunks;         // ceil(V / CH)
   int kk_full;         // ceil(n_sel / kSelWarps): lane-maximum rounds of the chunk threshold
+  int pdl;             // launched with programmatic stream serialization: rows are requested before griddepcontrol.wait
   int tma_rows;        // 1: full-scorer rows are 16-byte aligned -> bulk copies; 0: plain loads
   int arena_floats;    // union buffer: row stages | candidate rows | selection scratch
   int rows_per_group;  // candidate rows that fit the arena
@@ -173,12 +174,10 @@ __device__ __noinline__ void group_affine_scan(const float* a, const float* b, f
 //   bR0[u] = r_sum[u-1]   and   bR1[u] = r^b[u-1]   for pstart <= u < T, LGASR_NEG elsewhere
 // (pstart = max(olen, 1) of THIS hypothesis): the phi arrays of the psi phase, shifted by one frame so that
 // phi[t-1] + x[t] is an aligned element-wise sum.  *psi_eos = r_sum[T-1].
-__device__ __forceinline__ void group_ctc_state(float* bR0, float* bR1, const float* bA, float* bB, const float* bC,
-                                                float* bD, float* __restrict__ r_out, int has_parent, int par_initial,
-                                                int same, int olen_par, int T, int Tp, int g, float* ws, float* psi_eos,
-                                                int bar_id, long long* tr) {
+__device__ __forceinline__ void group_ctc_scans(const float* bR1, const float* bA, float* bB, const float* bC, float* bD,
+                                                int has_parent, int par_initial, int same, int olen_par, int T, int g,
+                                                float* ws, int bar_id, long long* tr) {
   const int start = olen_par > 1 ? olen_par : 1;           // first frame of the recursion that makes this state
-  const int pstart = olen_par + 1 > 1 ? olen_par + 1 : 1;  // max(olen, 1) of this hypothesis
   float rn0 = LGASR_LOGZERO;
   if (has_parent) {
     const int start_par = olen_par - 1 > 1 ? olen_par - 1 : 1;  // the parent's own recursion start
@@ -198,8 +197,18 @@ __device__ __forceinline__ void group_ctc_state(float* bR0, float* bR1, const fl
     group_affine_scan(bC, bB, bD, start, T, rn0, g, ws, bar_id);
     if (tr && g == 0) tr[9] = clock64();
   }
+}
+
+// second half, by ALL threads of the CTA after the groups have joined: write the state to global memory and
+// lay out the shifted phi arrays of the psi phase (see above).  Ends with a CTA barrier.
+__device__ __forceinline__ void cta_ctc_epilogue(float* bR0, float* bR1, const float* bA, float* bB, const float* bC,
+                                                 float* bD, float* __restrict__ r_out, int has_parent, int olen_par, int T,
+                                                 int Tp, int tid, float* psi_eos) {
+  const int start = olen_par > 1 ? olen_par : 1;
+  const int pstart = olen_par + 1 > 1 ? olen_par + 1 : 1;  // max(olen, 1) of this hypothesis
+  const float rn0 = (has_parent && olen_par == 0) ? bA[0] : LGASR_LOGZERO;
 #pragma unroll 1
-  for (int u = g; u <= Tp; u += kCtcThreads) {
+  for (int u = tid; u <= Tp; u += kStepThreads) {
     const int t = u - 1;  // state of frame t
     float rn = LGASR_LOGZERO, rs = LGASR_LOGZERO, rb = LGASR_LOGZERO;
     if (t >= 0 && t < T) {
@@ -228,12 +237,13 @@ __device__ __forceinline__ void group_ctc_state(float* bR0, float* bR1, const fl
       o1[u] = in ? rb : LGASR_NEG;
     }
   }
+  __syncthreads();
   if (!has_parent) {
-    group_bar(bar_id, kCtcThreads);
-    for (int u = g; u < Tp; u += kCtcThreads) {
+    for (int u = tid; u < Tp; u += kStepThreads) {
       bR0[u] = bB[u];
       bR1[u] = bD[u];
     }
+    __syncthreads();
   }
 }
 
@@ -377,7 +387,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     S->w_eos = 0.f;
     S->psi_eos = 0.f;
     mbar_fence_init();
-    if (tma && mode != kModeFullCtc) {
+    if (sl.pdl && tma && mode != kModeFullCtc) {
       const int pre = nchunks < NST ? nchunks : NST;
       for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
     }
@@ -390,10 +400,11 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   const int4 rm = d.rmeta[pp][row];  // parent slot, last token, parent's last token
   const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
   const float hyp_score = d.score[pp][row];
+  const int maxlen_b = d.maxlen[b], minlen_b = d.minlen[b];  // for the selection (no dependent load there)
   if (done || h >= n_run) {
     if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
     // the row copies already in flight target this CTA's shared memory: let them land before leaving
-    if (tid == kCtcThreads && tma && mode != kModeFullCtc) {
+    if (tid == kCtcThreads && sl.pdl && tma && mode != kModeFullCtc) {
       const int pre = nchunks < NST ? nchunks : NST;
       for (int c = 0; c < pre; ++c) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[c]), 0);
     }
@@ -421,6 +432,9 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         bulk_g2s(bC, xT_b + (long long)d.blank * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
       }
     }
+  } else if (tid == kCtcThreads && !sl.pdl && tma && mode != kModeFullCtc) {
+    const int pre = nchunks < NST ? nchunks : NST;
+    for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
   }
   __syncthreads();
   LGASR_TR(0, 0);
@@ -432,9 +446,8 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     if (d.use_ctc) {
       mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
       LGASR_TR(0, 1);
-      float* r_out = d.r[rp ^ 1] + ((long long)row * 2) * Tp;
-      group_ctc_state(bR0, bR1, bA, bB, bC, bD, r_out, has_parent, step == 1, last == rm.z, olen - 1, T, Tp, tid, S->ws,
-                      &S->psi_eos, kBarCtc, TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
+      group_ctc_scans(bR1, bA, bB, bC, bD, has_parent, step == 1, last == rm.z, olen - 1, T, tid, S->ws, kBarCtc,
+                      TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
       LGASR_TR(0, 2);
     }
   } else if (mode != kModeFullCtc) {
@@ -632,6 +645,9 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
       issue_cand_rows(d, S->keys[cur], 0, n_top < sl.rows_per_group ? n_top : sl.rows_per_group, xT_b, arena, S, lane);
   }
   __syncthreads();
+  if (d.use_ctc)
+    cta_ctc_epilogue(bR0, bR1, bA, bB, bC, bD, d.r[rp ^ 1] + ((long long)row * 2) * Tp, has_parent, olen - 1, T, Tp, tid,
+                     &S->psi_eos);
   LGASR_TR(0, 3);
 
   // ======================= all warps: candidate records ===============================================
@@ -763,7 +779,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   LGASR_TR(0, 6);
   LGASR_GT(15);
   if (!S->last_flag) return;
-  utt_select(d, tm, b, pp, step, arena, n_run, cur_len, TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
+  utt_select(d, tm, b, pp, step, arena, n_run, cur_len, maxlen_b, minlen_b, TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
   LGASR_TR(0, 7);
   LGASR_GT(15);
 }
