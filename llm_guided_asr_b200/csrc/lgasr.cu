@@ -55,6 +55,8 @@ struct lgasr_handle {
   std::vector<long long> primer;
   std::vector<int> xlens;
   int* h_pin;  // pinned staging: n_run[B], done[B]
+  int* h_begin_pin;  // pinned staging of lgasr_begin: maxlen[B], minlen[B], primer (int64)
+  cudaEvent_t ev_begin;  // the copies out of h_begin_pin have been performed
   long long* d_primer;
   float* d_logp_stage;  // staging for set_posteriors_host
   size_t logp_stage_elems;
@@ -305,6 +307,8 @@ extern "C" int lgasr_destroy(lgasr_handle* h) {
     cudaEventDestroy(h->rg_ev[1]);
   }
   if (h->h_pin) cudaFreeHost(h->h_pin);
+  if (h->h_begin_pin) cudaFreeHost(h->h_begin_pin);
+  if (h->ev_begin) cudaEventDestroy(h->ev_begin);
   if (h->d_logp_stage) cudaFree(h->d_logp_stage);
   for (int s = 0; s < 2; ++s) {
     for (int k = 0; k < LGASR_MAX_TERMS; ++k)
@@ -329,7 +333,7 @@ extern "C" int lgasr_set_posteriors(lgasr_handle* h, const float* d_logp, const 
   CK(cudaMemcpyAsync(const_cast<int*>(d.xlen), h->xlens.data(), sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
   if (d.use_ctc) {
     if (!d_logp) return fail(LGASR_EINVAL, "null posteriors");
-    dim3 grid((d.V + 31) / 32, (d.Tp + 31) / 32, d.B), block(32, 8);
+    dim3 grid((d.V + 63) / 64, (d.Tp + 63) / 64, d.B), block(32, 8);
     k_transpose_pad<<<grid, block, 0, st>>>(d_logp, const_cast<float*>(d.xT), d.xlen, d.T, d.Tp, d.V, d.blank, 0);
     LAUNCH_CK();
   }
@@ -368,21 +372,36 @@ extern "C" int lgasr_begin(lgasr_handle* h, const int32_t* h_maxlen, const int32
   for (int b = 0; b < d.B; ++b)
     if (h_maxlen[b] > d.maxlen_cap) return fail(LGASR_EINVAL, "maxlen[%d]=%d > cap %d", b, h_maxlen[b], d.maxlen_cap);
   h->primer.assign(h_primer, h_primer + h->cfg.primer_len);
-  CK(cudaMemcpyAsync(const_cast<int*>(d.maxlen), h_maxlen, sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(const_cast<int*>(d.minlen), h_minlen, sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(h->d_primer, h->primer.data(), sizeof(long long) * h->cfg.primer_len, cudaMemcpyHostToDevice, st));
+  // the host arrays are staged in pinned memory owned by the handle, so the call does not have to
+  // synchronise the stream before returning
+  const int P = h->cfg.primer_len;
+  if (!h->h_begin_pin) {
+    if (cudaMallocHost(&h->h_begin_pin, sizeof(int) * 2 * d.B + sizeof(long long) * (P + 1)) != cudaSuccess)
+      return fail(LGASR_ENOMEM, "cudaMallocHost");
+    CK(cudaEventCreateWithFlags(&h->ev_begin, cudaEventDisableTiming));
+  } else {
+    CK(cudaEventSynchronize(h->ev_begin));  // the previous begin's copies have left the staging buffer
+  }
+  int* pin_i = h->h_begin_pin;
+  long long* pin_p = reinterpret_cast<long long*>(pin_i + 2 * d.B + ((2 * d.B) & 1));
+  memcpy(pin_i, h_maxlen, sizeof(int) * d.B);
+  memcpy(pin_i + d.B, h_minlen, sizeof(int) * d.B);
+  memcpy(pin_p, h_primer, sizeof(long long) * P);
+  CK(cudaMemcpyAsync(const_cast<int*>(d.maxlen), pin_i, sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(const_cast<int*>(d.minlen), pin_i + d.B, sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(h->d_primer, pin_p, sizeof(long long) * P, cudaMemcpyHostToDevice, st));
+  CK(cudaEventRecord(h->ev_begin, st));
   if (d.use_ctc) {
     const long long n = (long long)d.B * d.W * 2 * d.Tp;
     k_fill<<<592, 256, 0, st>>>(d.r[0], n, LGASR_LOGZERO);
     LAUNCH_CK();
     k_fill<<<592, 256, 0, st>>>(d.r[1], n, LGASR_LOGZERO);
     LAUNCH_CK();
-    k_ctc_init_state<<<d.B, 32, 0, st>>>(d.xT, d.r[0], d.T, d.Tp, d.V, d.W, d.blank, d.W);
+    k_ctc_init_state<<<d.B, 128, d.Tp * sizeof(float), st>>>(d.xT, d.r[0], d.T, d.Tp, d.V, d.W, d.blank, d.W);
     LAUNCH_CK();
   }
   k_begin<<<d.B, 128, 0, st>>>(d, h->d_primer, h->cfg.primer_len);
   LAUNCH_CK();
-  CK(cudaStreamSynchronize(st));  // host arrays above may be reused by the caller
   h->pp = 0;
   h->rp = 0;
   h->step = 0;
@@ -776,7 +795,7 @@ extern "C" int lgasr_decode_replay_host(lgasr_handle* h, const float* h_logp, co
 extern "C" int lgasr_transpose_posteriors(const float* d_logp, int T, int V, int xlen, int blank, float* d_xT, int Tp,
                                           void* stream) {
   if (!d_logp || !d_xT || T < 1 || V < 1 || Tp < T) return fail(LGASR_EINVAL, "bad argument");
-  dim3 grid((V + 31) / 32, (Tp + 31) / 32, 1), block(32, 8);
+  dim3 grid((V + 63) / 64, (Tp + 63) / 64, 1), block(32, 8);
   k_transpose_pad<<<grid, block, 0, (cudaStream_t)stream>>>(d_logp, d_xT, nullptr, T, Tp, V, blank, xlen);
   LAUNCH_CK();
   return LGASR_OK;
@@ -785,7 +804,7 @@ extern "C" int lgasr_transpose_posteriors(const float* d_logp, int T, int V, int
 extern "C" int lgasr_ctc_initial_state(const float* d_xT, int T, int Tp, int blank, float* d_r0, void* stream) {
   if (!d_xT || !d_r0 || T < 1 || Tp < T) return fail(LGASR_EINVAL, "bad argument");
   // V is only used for the per-utterance stride; one utterance here
-  k_ctc_init_state<<<1, 32, 0, (cudaStream_t)stream>>>(d_xT, d_r0, T, Tp, 0, 1, blank, 1);
+  k_ctc_init_state<<<1, 128, Tp * sizeof(float), (cudaStream_t)stream>>>(d_xT, d_r0, T, Tp, 0, 1, blank, 1);
   LAUNCH_CK();
   return LGASR_OK;
 }

@@ -691,29 +691,43 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
 
 // ------------------------------------------------------------------------------------------
 // x[B][T][V] -> xT[B][V][Tp] with the padding rule of CTCPrefixScoreTH.__init__ (:46-49)
-__global__ void k_transpose_pad(const float* __restrict__ x, float* __restrict__ xT, const int* __restrict__ xlen,
-                                int T, int Tp, int V, int blank, int xlen_scalar) {
-  __shared__ float tile[32][33];
+// 64 x 64 tiles, block (32, 8): 16 independent coalesced loads, then 16 coalesced stores per thread.
+__global__ void __launch_bounds__(256) k_transpose_pad(const float* __restrict__ x, float* __restrict__ xT,
+                                                       const int* __restrict__ xlen, int T, int Tp, int V, int blank,
+                                                       int xlen_scalar) {
+  __shared__ float tile[64][65];
   const int b = blockIdx.z;
-  const int v0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
-  const int len = xlen ? xlen[b] : xlen_scalar;
+  const int v0 = blockIdx.x * 64, t0 = blockIdx.y * 64;
+  const int len = min(xlen ? xlen[b] : xlen_scalar, T);
   const float* xb = x + (long long)b * T * V;
   float* xo = xT + (long long)b * V * Tp;
-  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    int t = t0 + i, v = v0 + threadIdx.x;
-    float val = LGASR_LOGZERO;
-    if (v < V) {
-      if (t < len && t < T)
-        val = xb[(long long)t * V + v];
-      else
-        val = (v == blank) ? 0.f : LGASR_LOGZERO;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  float val[16];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int t = t0 + ty + 8 * k;
+#pragma unroll
+    for (int hv = 0; hv < 2; ++hv) {
+      const int v = v0 + tx + 32 * hv;
+      float r = (v == blank) ? 0.f : LGASR_LOGZERO;  // padding rule of ctc_prefix_score.py:46-49
+      if (v < V && t < len) r = __ldcs(xb + (long long)t * V + v);
+      val[2 * k + hv] = r;
     }
-    tile[i][threadIdx.x] = val;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    tile[ty + 8 * k][tx] = val[2 * k];
+    tile[ty + 8 * k][tx + 32] = val[2 * k + 1];
   }
   __syncthreads();
-  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    int v = v0 + i, t = t0 + threadIdx.x;
-    if (v < V && t < Tp) xo[(long long)v * Tp + t] = tile[threadIdx.x][i];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int v = v0 + ty + 8 * k;
+    if (v < V) {
+      const int t = t0 + tx;
+      if (t < Tp) xo[(long long)v * Tp + t] = tile[tx][ty + 8 * k];
+      if (t + 32 < Tp) xo[(long long)v * Tp + t + 32] = tile[tx + 32][ty + 8 * k];
+    }
   }
 }
 
@@ -728,13 +742,20 @@ __global__ void k_ctc_init_state(const float* __restrict__ xT, float* __restrict
   const int b = blockIdx.x;
   const float* x0 = xT + ((long long)b * V + blank) * Tp;
   float* r = r0 + (long long)b * per_utt_stride_rows * 2 * Tp;
-  if (threadIdx.x == 0) {
+  extern __shared__ float cs[];  // [Tp]
+  for (int t = threadIdx.x; t < T; t += blockDim.x) cs[t] = x0[t];  // all loads in flight at once
+  __syncthreads();
+  if (threadIdx.x == 0) {  // the sum itself stays sequential: same fp32 roundings as torch.cumsum on the CPU
     float acc = 0.f;
     for (int t = 0; t < T; ++t) {
-      acc = __fadd_rn(acc, x0[t]);
-      r[t] = LGASR_LOGZERO;
-      r[Tp + t] = acc;
+      acc = __fadd_rn(acc, cs[t]);
+      cs[t] = acc;
     }
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < T; t += blockDim.x) {
+    r[t] = LGASR_LOGZERO;
+    r[Tp + t] = cs[t];
   }
 }
 
