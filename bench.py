@@ -364,6 +364,7 @@ def run_ours(args, rank, world, local_rank):
         "config": bench_config(cfg),
         "rtfx": value * AUDIO_SEC,
         "us_per_position": ms_step * 1e3 / L,
+        "k_step": eng.launch_info(),
         "positions_run": len(n_run_hist),
         "e2e": {
             "value": e2e_val, "unit": "utts/s",

@@ -128,6 +128,12 @@ int lgasr_gather_ended(lgasr_handle* h, int utt, int32_t* n_ended, int32_t* max_
 int lgasr_set_profiling(lgasr_handle* h, int on);
 int lgasr_get_profile(lgasr_handle* h, float* ms_score_rows, float* ms_select, int32_t* n_steps);
 
+/* Launch geometry of the fused step kernel chosen for this handle (bench.py reports it): cluster = 1 when the
+ * `beam` CTAs of an utterance are launched as one thread-block cluster (records exchanged through distributed
+ * shared memory), 0 for the ticket variant (records through L2); dynamic shared memory per CTA; floats per
+ * staged row chunk; stages. */
+int lgasr_launch_info(lgasr_handle* h, int32_t* cluster, int32_t* smem_bytes, int32_t* chunk_floats, int32_t* stages);
+
 /* Debug time line of the fused step kernel: when the environment variable LGASR_TRACE is set at
  * lgasr_create, every CTA of k_step stamps clock64() at its phase boundaries; this copies the
  * [B][beam][2 groups][16] stamps of the most recent step to h_out (n = capacity in elements). */

@@ -51,6 +51,7 @@ struct lgasr_handle {
   size_t smem_step;
   int ept;           // 8 or 16 elements per selection thread and chunk
   int fused;         // 1: one k_step launch per position; 0: k_score_rows + k_select
+  int cluster;       // 1: k_step is launched as clusters of `beam` CTAs (records through distributed shared memory)
   std::vector<void*> allocs;
   std::vector<long long> primer;
   std::vector<int> xlens;
@@ -196,7 +197,10 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     if (rpg < 1) rpg = 1;
     if (rpg > n_sel) rpg = n_sel;
     sl.rows_per_group = rpg;
+    const char* ncl = getenv("LGASR_NO_CLUSTER");
+    h->cluster = h->fused && d.W >= 2 && d.W <= 16 && !(ncl && ncl[0] == '1');
     h->smem_step = sizeof(StepSmem) + (size_t)6 * d.Tp * sizeof(float) + (size_t)arena * sizeof(float);
+    if (h->cluster) h->smem_step += (size_t)utt_select_smem_floats(d.W, d.R, d.NS) * sizeof(float);
     if (h->fused && h->smem_step > 220 * 1024) {
       delete h;
       return fail(LGASR_EINVAL, "shared memory need too large for the fused step (T=%d beam=%d K=%d)", d.T, d.W, d.K);
@@ -279,9 +283,40 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     }
     static size_t cur_step = 0;
     if (e == cudaSuccess && h->fused && h->smem_step > cur_step) {
-      e = cudaFuncSetAttribute(k_step<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      e = cudaFuncSetAttribute(k_step<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
       if (e == cudaSuccess) cur_step = h->smem_step;
+    }
+    if (e == cudaSuccess && h->cluster) {
+      static bool np_set = false;
+      if (!np_set) {
+        e = cudaFuncSetAttribute(k_step<false, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        np_set = (e == cudaSuccess);
+      }
+      // can at least one cluster of `beam` CTAs be resident?  otherwise fall back to the ticket variant
+      int ncl_max = 0;
+      cudaLaunchConfig_t qc = {};
+      qc.gridDim = dim3(d.W, d.B);
+      qc.blockDim = dim3(kStepThreads);
+      qc.dynamicSmemBytes = h->smem_step;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = d.W;
+      qa[0].val.clusterDim.y = 1;
+      qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa;
+      qc.numAttrs = 1;
+      // clusters only pay while every utterance's cluster is resident at once (one wave): with more utterances
+      // than that, whole-cluster scheduling leaves CTA slots idle (measured: 113 vs 94 us per launch at B = 512)
+      if (e != cudaSuccess || cudaOccupancyMaxActiveClusters(&ncl_max, k_step<false, true>, &qc) != cudaSuccess ||
+          ncl_max < d.B) {
+        cudaGetLastError();
+        e = cudaSuccess;
+        h->cluster = 0;
+      }
     }
     if (e == cudaSuccess && h->smem_sel > cur_sel) {
       e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_sel);
@@ -453,16 +488,34 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     cfg.blockDim = dim3(kStepThreads);
     cfg.dynamicSmemBytes = h->smem_step;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (pdl) {
+      at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
+    if (h->cluster) {
+      at[na].id = cudaLaunchAttributeClusterDimension;
+      at[na].val.clusterDim.x = d.W;
+      at[na].val.clusterDim.y = 1;
+      at[na].val.clusterDim.z = 1;
+      ++na;
+    }
     cfg.attrs = at;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = na;
     sl.pdl = pdl ? 1 : 0;
-    if (d.trace)
-      CK(cudaLaunchKernelEx(&cfg, k_step<true>, d, tm, sl, h->pp, h->rp, h->step));
-    else
-      CK(cudaLaunchKernelEx(&cfg, k_step<false>, d, tm, sl, h->pp, h->rp, h->step));
+    if (h->cluster) {
+      if (d.trace)
+        CK(cudaLaunchKernelEx(&cfg, k_step<true, true>, d, tm, sl, h->pp, h->rp, h->step));
+      else
+        CK(cudaLaunchKernelEx(&cfg, k_step<false, true>, d, tm, sl, h->pp, h->rp, h->step));
+    } else {
+      if (d.trace)
+        CK(cudaLaunchKernelEx(&cfg, k_step<true, false>, d, tm, sl, h->pp, h->rp, h->step));
+      else
+        CK(cudaLaunchKernelEx(&cfg, k_step<false, false>, d, tm, sl, h->pp, h->rp, h->step));
+    }
     LAUNCH_CK();
     if (h->profiling) {
       CK(cudaEventRecord(pe[1], st));
@@ -494,6 +547,15 @@ extern "C" int lgasr_step(lgasr_handle* h, const float* const* h_term_ptr, const
   Terms tm;
   TRY(fill_terms(h, tm, h_term_ptr, h_term_const, h_term_weight, ld));
   return step_impl(h, tm, (cudaStream_t)stream);
+}
+
+extern "C" int lgasr_launch_info(lgasr_handle* h, int32_t* cluster, int32_t* smem_bytes, int32_t* chunk_floats, int32_t* stages) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  if (cluster) *cluster = h->fused ? h->cluster : 0;
+  if (smem_bytes) *smem_bytes = (int32_t)(h->fused ? h->smem_step : h->smem_rows);
+  if (chunk_floats) *chunk_floats = h->sl.CH;
+  if (stages) *stages = h->sl.NST;
+  return LGASR_OK;
 }
 
 extern "C" int lgasr_set_profiling(lgasr_handle* h, int on) {

@@ -359,6 +359,9 @@ __host__ __device__ inline long long utt_select_smem_floats(int W, int R, int NS
   return (long long)W * R * 3 + 2LL * W + (long long)W * (3 + NS) + 2LL * W + 3LL * kSelListCap + 8;
 }
 
+// PRE: the records and the parents' fields are already in `smem` (written there through distributed shared
+// memory by the CTAs of the cluster, k_step<.., true>); otherwise they are fetched from global memory.
+template <bool PRE>
 __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b, int pp, int step, float* smem, int n_run,
                                            int cur_len, int maxlen, int minlen, long long* tr = nullptr) {
   const int tid = threadIdx.x, nthr = blockDim.x;
@@ -393,6 +396,23 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
   if (tid < W) rowmax[tid] = 0u;
   if (tid == 0) *sh_cnt = 0;
   if (prefilter) __syncthreads();
+  if (PRE) {
+    if (tid == 0) {
+      n_end0 = d.n_ended[b];
+      best_all0 = d.best_all[b];
+      bbl_new0 = bbl[new_len];
+#pragma unroll
+      for (int m = 0; m < 3; ++m) {
+        const int len = step - m;
+        if (len >= 0 && len <= d.Lcap + 1) bbl_m[m] = bbl[len];
+      }
+    }
+    if (prefilter)
+      for (int e = tid; e < nrec; e += nthr) {
+        const unsigned long long ke = r_key[e];
+        if (ke) atomicMax(rowmax + e / n_rec_row, (unsigned)(ke >> 32));
+      }
+  } else {
   // first pass of both loops: every global load is issued before anything is consumed (one round trip)
   const int npar = n_run * (3 + NS);
   int tok0 = -1, h0 = 0;
@@ -456,6 +476,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
     else if (f == 2) v = __float_as_uint(d.s_prev[pp][prow]);
     else v = __float_as_uint(d.scores[pp][(long long)prow * NS + (f - 3)]);
     put_parent(h, f, v);
+  }
   }
   if (tid < W) sel[tid] = -1;
   __syncthreads();
@@ -686,7 +707,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
     if (threadIdx.x == 0) utt_carry_done(d, b, pp);
     return;
   }
-  utt_select(d, tm, b, pp, step, smem, d.n_run[pp][b], d.cur_len[pp][b], d.maxlen[b], d.minlen[b]);
+  utt_select<false>(d, tm, b, pp, step, smem, d.n_run[pp][b], d.cur_len[pp][b], d.maxlen[b], d.minlen[b]);
 }
 
 // ------------------------------------------------------------------------------------------

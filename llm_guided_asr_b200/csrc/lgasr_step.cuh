@@ -278,6 +278,22 @@ __device__ __forceinline__ long long gtimer() {
     if (TR && tid == 0) d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 + (i)] = gtimer(); \
   } while (0)
 
+// ---- thread-block cluster helpers (one cluster = the `beam` CTAs of an utterance) -------------------------
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// shared::cluster address of `p` (an address in this CTA's shared memory) in the CTA of rank `rank`
+__device__ __forceinline__ uint32_t map_rank(const void* p, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster(uint32_t addr, unsigned long long v) {
+  asm volatile("st.shared::cluster.u64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_cluster(uint32_t addr, unsigned v) {
+  asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
 constexpr int kBarCtc = 1, kBarSel = 2;  // named barriers of the two groups (0 = __syncthreads)
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -350,7 +366,10 @@ __device__ __forceinline__ float4 fused4(const Terms& tm, const float* sb, int C
   return acc;
 }
 
-template <bool TR>
+// CL: launched as clusters of `beam` CTAs (cluster rank == hypothesis slot): the candidate records and the
+// parents' fields travel to the shared memory of the rank-0 CTA (distributed shared memory) and a cluster
+// barrier replaces the fence + atomic ticket and the exchange through L2; rank 0 runs the selection.
+template <bool TR, bool CL>
 __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepLaunch sl, int pp, int rp, int step) {
   const int b = blockIdx.y, h = blockIdx.x;
   const int tid = threadIdx.x;
@@ -375,6 +394,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   // k_step), so under PDL it overlaps the previous position's selection tail: the next grid's CTAs take the
   // slots of CTAs that have left and have their score rows in flight before the previous grid has drained.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (CL) cluster_arrive();  // phase 1: "this CTA runs"; waited for before the first remote store
   if (tid == kCtcThreads) {
 #pragma unroll
     for (int i = 0; i < kMaxStages; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_full[i]), 1);
@@ -401,12 +421,20 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
   const float hyp_score = d.score[pp][row];
   const int maxlen_b = d.maxlen[b], minlen_b = d.minlen[b];  // for the selection (no dependent load there)
+  // cluster variant: this hypothesis' fields the selection needs of its parents, sent to rank 0 later
+  const int my_slot = CL ? d.run_slot[pp][row] : 0;
+  const float my_sc = (CL && tid < d.NS) ? d.scores[pp][(long long)row * d.NS + tid] : 0.f;
   if (done || h >= n_run) {
     if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
     // the row copies already in flight target this CTA's shared memory: let them land before leaving
     if (tid == kCtcThreads && sl.pdl && tma && mode != kModeFullCtc) {
       const int pre = nchunks < NST ? nchunks : NST;
       for (int c = 0; c < pre; ++c) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[c]), 0);
+    }
+    if (CL) {  // an idle CTA still takes part in both phases of the cluster barrier
+      __syncwarp();
+      cluster_wait();
+      cluster_arrive();
     }
     return;
   }
@@ -657,6 +685,34 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   float* c_total = d.cand_total + (long long)row * R;
   int* c_tok = d.cand_tok + (long long)row * R;
   float* c_psi = d.cand_psi + (long long)row * R;
+  // selection buffer of the cluster's rank-0 CTA (layout of utt_select): keys [W*R] u64 | psi [W*R] | sel, dest
+  // [2W] | p_slot, p_last, p_sprev [3W] | p_scores [W*NS]
+  float* selbuf = arena + sl.arena_floats;
+  const uint32_t sel0 = CL ? map_rank(selbuf, 0) : 0u;
+  if (CL) {
+    cluster_wait();  // phase 1: every CTA of the cluster is running, its shared memory may be written
+    const int WR = W * R;
+    if (tid == 0) {
+      st_cluster(sel0 + 4u * (3 * WR + 2 * W + h), (unsigned)my_slot);
+      st_cluster(sel0 + 4u * (3 * WR + 3 * W + h), (unsigned)last);
+      st_cluster(sel0 + 4u * (3 * WR + 4 * W + h), __float_as_uint(s_prev));
+    }
+    if (tid < d.NS) st_cluster(sel0 + 4u * (3 * WR + 5 * W + h * d.NS + tid), __float_as_uint(my_sc));
+  }
+  auto put_rec = [&](int jr, float total, int tok, float psi) {
+    if (CL) {
+      const int e = h * R + jr;
+      unsigned u = __float_as_uint(total + 0.0f);
+      u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+      const unsigned long long ke = tok >= 0 ? (((unsigned long long)u << 32) | (unsigned)(~(h * V + tok))) : 0ull;
+      st_cluster(sel0 + 8u * e, ke);
+      st_cluster(sel0 + 4u * (2 * W * R + e), __float_as_uint(psi));
+    } else {
+      c_total[jr] = total;
+      c_tok[jr] = tok;
+      c_psi[jr] = psi;
+    }
+  };
 
   if (mode == kModeNoCtc) {
     if (lane == 0) {
@@ -668,9 +724,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           const float wfull = (d.key < 0) ? key_val(tk[jr]) : fuse_at(tm, rowoff, c);
           total = __fadd_rn(wfull, hyp_score);
         }
-        c_total[jr] = total;
-        c_tok[jr] = c;
-        c_psi[jr] = 0.f;
+        put_rec(jr, total, c, 0.f);
       }
     }
   } else {
@@ -728,18 +782,14 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           psi = LGASR_LOGZERO;  // :183-185
         if (have && hl == 0) {
           const float wfull = (d.key < 0) ? key_val(tk[jr]) : fuse_at(tm, rowoff, c);
-          c_total[jr] = __fadd_rn(__fadd_rn(wfull, __fmul_rn(d.w_ctc, __fsub_rn(psi, s_prev))), hyp_score);
-          c_tok[jr] = c;
-          c_psi[jr] = psi;
+          put_rec(jr, __fadd_rn(__fadd_rn(wfull, __fmul_rn(d.w_ctc, __fsub_rn(psi, s_prev))), hyp_score), c, psi);
         }
       }
     }
     if (lane == 0) {
       // unused pre-beam slots (fewer than S tokens in the vocabulary)
       for (int jr = n_top + warp; jr < n_sel; jr += kStepWarps) {
-        c_total[jr] = -INFINITY;
-        c_tok[jr] = -1;
-        c_psi[jr] = 0.f;
+        put_rec(jr, -INFINITY, -1, 0.f);
       }
     }
     if (warp == kStepWarps - 1) {
@@ -753,9 +803,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           const float wfull = (d.key < 0) ? S->w_eos : fuse_at(tm, rowoff, d.eos);
           total = __fadd_rn(__fadd_rn(wfull, __fmul_rn(d.w_ctc, __fsub_rn(psi_eos, s_prev))), hyp_score);
         }
-        c_total[n_sel] = total;
-        c_tok[n_sel] = dup ? -1 : d.eos;
-        c_psi[n_sel] = psi_eos;
+        put_rec(n_sel, total, dup ? -1 : d.eos, psi_eos);
       }
     }
   }
@@ -764,22 +812,35 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   // CTA barrier, then ONE fence + atomic by thread 0 (the cooperative-groups grid-sync pattern): the
   // barrier orders every warp's record stores before thread 0's cumulative gpu-scope fence.
   LGASR_TR(0, 5);
-  __syncthreads();
-  if (tid == 0) {
-    __threadfence();
-    const int old = atomicAdd(d.arrive + b, 1);
-    const int is_last = (old == n_run - 1) ? 1 : 0;
-    if (is_last) {
+  if (CL) {
+    // phase 2: every thread's remote stores are released by its own arrive; only rank 0 waits
+    __syncwarp();
+    cluster_arrive();
+    LGASR_TR(0, 6);
+    LGASR_GT(15);
+    if (h != 0) return;
+    cluster_wait();
+    utt_select<true>(d, tm, b, pp, step, selbuf, n_run, cur_len, maxlen_b, minlen_b,
+                     TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
+  } else {
+    __syncthreads();
+    if (tid == 0) {
       __threadfence();
-      d.arrive[b] = 0;
+      const int old = atomicAdd(d.arrive + b, 1);
+      const int is_last = (old == n_run - 1) ? 1 : 0;
+      if (is_last) {
+        __threadfence();
+        d.arrive[b] = 0;
+      }
+      S->last_flag = is_last;
     }
-    S->last_flag = is_last;
+    __syncthreads();
+    LGASR_TR(0, 6);
+    LGASR_GT(15);
+    if (!S->last_flag) return;
+    utt_select<false>(d, tm, b, pp, step, arena, n_run, cur_len, maxlen_b, minlen_b,
+                      TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
   }
-  __syncthreads();
-  LGASR_TR(0, 6);
-  LGASR_GT(15);
-  if (!S->last_flag) return;
-  utt_select(d, tm, b, pp, step, arena, n_run, cur_len, maxlen_b, minlen_b, TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
   LGASR_TR(0, 7);
   LGASR_GT(15);
 }

@@ -179,6 +179,12 @@ class FusedStepEngine:
                 )
             )
 
+    def launch_info(self) -> dict:
+        """Geometry of the fused step kernel of this handle (``lgasr_launch_info``)."""
+        v = [C.c_int32() for _ in range(4)]
+        _lib.check(self.lib.lgasr_launch_info(self._h, *[C.byref(x) for x in v]))
+        return dict(cluster=bool(v[0].value), smem_bytes=v[1].value, chunk_floats=v[2].value, stages=v[3].value)
+
     def set_profiling(self, on: bool):
         _lib.check(self.lib.lgasr_set_profiling(self._h, 1 if on else 0))
 

@@ -33,7 +33,7 @@ for B in Bs:
     us = min(ts[1:]) * 1e3 / L
     nrun = [[1] * B] + [[W] * B] * (L - 1)
     ab = bench.algorithmic_bytes(dict(cfg, B=B), nrun) / L
-    print(f"B={B:4d}  {us:8.2f} us/launch  algorithmic {ab / 1e6:7.1f} MB/launch  {ab / us / 1e3:7.1f} GB/s  frac {ab / us / 1e3 / peak:.3f}", flush=True)
+    print(f"B={B:4d}  {us:8.2f} us/launch  algorithmic {ab / 1e6:7.1f} MB/launch  {ab / us / 1e3:7.1f} GB/s  frac {ab / us / 1e3 / peak:.3f}  {eng.launch_info()}", flush=True)
     eng.close()
     del logp, tables, mats
     torch.cuda.empty_cache()

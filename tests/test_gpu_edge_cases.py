@@ -55,7 +55,13 @@ def _case(seed, T, V, beam, ntok, weights, with_lm, key="full", maxr=0.0):
     return nbest, ref
 
 
-def test_large_vocab_two_matrices_multi_chunk():
+@pytest.mark.parametrize("no_cluster", ["0", "1"])
+def test_large_vocab_two_matrices_multi_chunk(monkeypatch, no_cluster):
+    monkeypatch.setenv("LGASR_NO_CLUSTER", no_cluster)
+    _large_vocab()
+
+
+def _large_vocab():
     """OWSM-like: V = 20000, beam 5, pre-beam 7, decoder + LM matrices -> 2 stages, 14 chunks per row."""
     nbest, ref = _case(21, 40, 20000, 5, 6, dict(decoder=0.7, ctc=0.3, lm=0.5, length_bonus=0.2), True)
     _check(nbest, ref)
@@ -66,8 +72,11 @@ def test_vocab_not_multiple_of_four_uses_plain_staging():
     _check(nbest, ref)
 
 
-def test_single_matrix_long_row_one_chunk():
-    """The bench shape in small: one scorer matrix, V = 5000 (one 20 KB chunk), beam 10."""
+@pytest.mark.parametrize("no_cluster", ["0", "1"])
+def test_single_matrix_long_row_one_chunk(monkeypatch, no_cluster):
+    """The bench shape in small: one scorer matrix, V = 5000 (one 20 KB chunk), beam 10; with the records
+    exchanged through distributed shared memory (cluster launch) and through L2 (ticket)."""
+    monkeypatch.setenv("LGASR_NO_CLUSTER", no_cluster)
     nbest, ref = _case(23, 60, 5000, 10, 8, dict(decoder=0.7, ctc=0.3), False, maxr=-12)
     _check(nbest, ref)
 
@@ -103,7 +112,13 @@ def test_all_equal_rows_overflow_rounds():
     _check(nbest, ref)
 
 
-def test_replay_host_equals_stepping_at_full_vocab_width():
+@pytest.mark.parametrize("no_cluster", ["0", "1"])
+def test_replay_host_equals_stepping_at_full_vocab_width(monkeypatch, no_cluster):
+    monkeypatch.setenv("LGASR_NO_CLUSTER", no_cluster)
+    _replay_host_equals_stepping()
+
+
+def _replay_host_equals_stepping():
     """Whole-batch replay from host buffers (graph + PDL launches, double-buffered copies) must give
     exactly what position-by-position stepping gives: B = 8 utterances, ragged lengths, V = 5000."""
     from llm_guided_asr_b200.engine import FusedStepEngine

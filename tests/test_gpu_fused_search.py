@@ -38,8 +38,11 @@ def build_search(g, device):
     )
 
 
+@pytest.mark.parametrize("no_cluster", ["0", "1"])
 @pytest.mark.parametrize("name", GOLDEN_NAMES)
-def test_fused_search_matches_reference_golden(name):
+def test_fused_search_matches_reference_golden(name, no_cluster, monkeypatch):
+    """Both record-exchange variants of k_step: cluster launch (distributed shared memory) and ticket (L2)."""
+    monkeypatch.setenv("LGASR_NO_CLUSTER", no_cluster)
     g = Golden(name)
     c = g.spec
     dev = torch.device("cuda:0")
