@@ -173,6 +173,14 @@ int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blank, int m, c
                            const int32_t* d_last, const int32_t* d_sel_hyp, const int32_t* d_sel_tok, int olen,
                            float* d_r_new, void* stream);
 
+/* Streaming extension = CTCPrefixScoreTH.extend_state (ctc_prefix_score.py:246-269) for n survivor states:
+ * d_r_old [n][2][Tp_old] valid for T_old frames -> d_r_new [n][2][Tp_new] valid for T_new >= T_old frames of the
+ * (extended) posteriors d_xT [V][Tp_new]: old frames copied, new frames r^n = log-zero and
+ * r^b[t] = r^b[t-1] + x[t, blank], added one frame at a time like the reference.  (extend_prob itself is
+ * lgasr_transpose_posteriors of the longer utterance plus a copy of the frames already held.) */
+int lgasr_ctc_extend_state(const float* d_xT, int T_old, int T_new, int Tp_old, int Tp_new, int blank, int n,
+                           const float* d_r_old, float* d_r_new, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -917,3 +917,14 @@ extern "C" int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blan
   LAUNCH_CK();
   return LGASR_OK;
 }
+
+extern "C" int lgasr_ctc_extend_state(const float* d_xT, int T_old, int T_new, int Tp_old, int Tp_new, int blank, int n,
+                                      const float* d_r_old, float* d_r_new, void* stream) {
+  if (!d_xT || !d_r_old || !d_r_new || n < 1 || T_old < 1 || T_new < T_old || Tp_old < T_old || Tp_new < T_new)
+    return fail(LGASR_EINVAL, "bad argument");
+  const size_t smem = (size_t)(T_new - T_old + 1) * sizeof(float);
+  if (smem > 48 * 1024) return fail(LGASR_EINVAL, "extension too long");
+  k_ctc_extend_state<<<n, 128, smem, (cudaStream_t)stream>>>(d_xT, T_old, T_new, Tp_old, Tp_new, blank, d_r_old, d_r_new);
+  LAUNCH_CK();
+  return LGASR_OK;
+}

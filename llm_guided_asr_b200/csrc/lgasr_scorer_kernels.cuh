@@ -75,4 +75,28 @@ __global__ void __launch_bounds__(32) k_ctc_select_state(const float* __restrict
                  smem, smem + Tp, smem + 2 * Tp, smem + 3 * Tp, lane);
 }
 
+// CTCPrefixScoreTH.extend_state (ctc_prefix_score.py:246-269): one block per survivor state
+__global__ void k_ctc_extend_state(const float* __restrict__ xT, int T_old, int T_new, int Tp_old, int Tp_new, int blank,
+                                   const float* __restrict__ r_old, float* __restrict__ r_new) {
+  extern __shared__ float xb[];  // blank posteriors of the new frames
+  const int i = blockIdx.x;
+  const float* ro = r_old + (long long)i * 2 * Tp_old;
+  float* rn = r_new + (long long)i * 2 * Tp_new;
+  const int start = T_old > 1 ? T_old : 1;
+  for (int t = threadIdx.x; t < Tp_new; t += blockDim.x) {
+    rn[t] = (t < start) ? ro[t] : LGASR_LOGZERO;
+    if (t < start) rn[Tp_new + t] = ro[Tp_old + t];
+    if (t >= T_new) rn[Tp_new + t] = LGASR_LOGZERO;
+    if (t >= start && t < T_new) xb[t - start] = xT[(long long)blank * Tp_new + t];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {  // sequential on purpose: the fp32 roundings of the reference's frame-by-frame loop
+    float acc = ro[Tp_old + start - 1];
+    for (int t = start; t < T_new; ++t) {
+      acc = __fadd_rn(acc, xb[t - start]);
+      rn[Tp_new + t] = acc;
+    }
+  }
+}
+
 }  // namespace lgasr

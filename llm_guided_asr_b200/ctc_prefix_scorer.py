@@ -13,7 +13,8 @@ Same constructor and methods as the reference class, so an *unmodified* referenc
 
 The fused search (``llm_guided_asr_b200.beam_search.BatchBeamSearch``) does not call these methods:
 it only takes ``.ctc`` and ``.eos`` from this object and runs the same device functions inside the
-fused step kernels.  Streaming extension (``extend_prob`` / ``extend_state``) is not implemented yet.
+fused step kernels.  ``extend_prob`` / ``extend_state`` are the streaming extension of the scorer API
+(``scorers/ctc.py:128-157``); the per-hypothesis state here is ``(r (2, Tp), s, T)``.
 """
 
 import ctypes as C
@@ -116,7 +117,7 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
             hyp = torch.as_tensor([int(i)], dtype=torch.int32, device=dev)
             tok = torch.as_tensor([int(new_id)], dtype=torch.int32, device=dev)
             r_new = self._select(r_prev, last, hyp, tok, olen)[0]
-            return r_new, log_psi[int(i), int(new_id)]
+            return r_new, log_psi[int(i), int(new_id)], self.impl["T"]
         if type(state) is tuple and len(state) == 2 and torch.is_tensor(state[0]) and state[0].dim() > 0:
             # non-batch API: (scores over the candidate ids, states over the candidate ids)
             sc, st = state
@@ -145,9 +146,46 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         r_new = self._select(r_prev, last, hyp, ids[0].to(torch.int32).contiguous(), olen)
         return (psi - prev_score).to(x.dtype), (psi, r_new)
 
-    # -- streaming (next) -------------------------------------------------------
+    # -- streaming (scorers/ctc.py:128-157 -> ctc_prefix_score.py:222-269) ------------------------
     def extend_prob(self, x: torch.Tensor):
-        raise NotImplementedError("streaming extend_prob is not implemented in the CUDA scorer yet")
+        """The utterance grew: ``x (T_new, D)`` is the encoder output so far.  Frames already held keep
+        their old posteriors (``ctc_prefix_score.py:239``), the new ones are appended."""
+        m = self.impl
+        logp = self.ctc.log_softmax(x.unsqueeze(0))[0].to(torch.float32).contiguous()
+        T_new, V = logp.shape
+        if T_new <= m["T"]:
+            return
+        dev = m["device"]
+        Tp = (T_new + 3) & ~3
+        xT = torch.empty(V, Tp, dtype=torch.float32, device=dev)
+        r0 = torch.empty(2, Tp, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(m["lib"].lgasr_transpose_posteriors(logp.data_ptr(), T_new, V, T_new, self.blank, xT.data_ptr(), Tp, _st(dev)))
+            xT[:, : m["T"]] = m["xT"][:, : m["T"]]
+            _lib.check(m["lib"].lgasr_ctc_initial_state(xT.data_ptr(), T_new, Tp, self.blank, r0.data_ptr(), _st(dev)))
+        m.update(xT=xT, r0=r0, T=T_new, Tp=Tp)
 
     def extend_state(self, state):
-        raise NotImplementedError("streaming extend_state is not implemented in the CUDA scorer yet")
+        """Per-hypothesis states ``(r (2, Tp_old), s, T_old)`` -> the same states over the extended frames:
+        r^n = log-zero and r^b[t] = r^b[t-1] + x[t, blank] on the new frames (``ctc_prefix_score.py:246-269``)."""
+        m = self.impl
+        dev = m["device"]
+        out = list(state)
+        groups = {}
+        for i, st in enumerate(state):
+            if st is None or st[2] >= m["T"]:
+                continue
+            groups.setdefault((st[2], st[0].shape[-1]), []).append(i)
+        for (T_old, Tp_old), idx in groups.items():
+            r_old = torch.stack([state[i][0] for i in idx]).contiguous()
+            r_new = torch.empty(len(idx), 2, m["Tp"], dtype=torch.float32, device=dev)
+            with torch.cuda.device(dev):
+                _lib.check(
+                    m["lib"].lgasr_ctc_extend_state(
+                        m["xT"].data_ptr(), T_old, m["T"], Tp_old, m["Tp"], self.blank, len(idx), r_old.data_ptr(),
+                        r_new.data_ptr(), _st(dev),
+                    )
+                )
+            for k, i in enumerate(idx):
+                out[i] = (r_new[k], state[i][1], m["T"])
+        return out

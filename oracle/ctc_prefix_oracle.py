@@ -110,6 +110,27 @@ class CTCPrefixOracle:
         scores = (log_psi - np.asarray(s_prev, dtype=np.float32).reshape(n, 1)).astype(np.float32)
         return scores, (r, log_psi, idmap)
 
+    # -- streaming (ctc_prefix_score.py:222-269) ---------------------------------------------------
+    def extend_prob(self, logp_new):
+        """``extend_prob``: the utterance grew to ``logp_new (T_new, V)``; the frames already held keep
+        their old posteriors (``self.x[:, :tmp_x.shape[1]] = tmp_x``, :239), the rest is appended."""
+        xn = np.array(logp_new, dtype=np.float32, copy=True)
+        if xn.shape[0] > self.T:
+            xn[: self.T] = self.x
+            self.x = xn
+            self.T = xn.shape[0]
+            self.end_frame = self.T - 1
+
+    def extend_state(self, r_prev):
+        """``extend_state``: ``r_prev (T_old, 2)`` -> ``(T, 2)``; new frames get r^n = logzero and
+        r^b[t] = r^b[t-1] + x[t, blank], added one frame at a time (:263-267)."""
+        r = np.full((self.T, 2), LOGZERO, dtype=np.float32)
+        start = max(r_prev.shape[0], 1)
+        r[:start] = r_prev[:start]
+        for t in range(start, self.T):
+            r[t, 1] = np.float32(r[t - 1, 1] + self.x[t, self.blank])
+        return r
+
     @staticmethod
     def select_state(state, h, tok):
         """Survivor state (``CTCPrefixScorer.select_state`` TH branch, ``scorers/ctc.py:56-62``)."""
