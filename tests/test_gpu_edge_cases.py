@@ -81,6 +81,13 @@ def test_single_matrix_long_row_one_chunk(monkeypatch, no_cluster):
     _check(nbest, ref)
 
 
+def test_long_peaky_utterance_full_length():
+    """configs[1] length (T = 374 frames) with peaky posteriors: the r values reach magnitudes where one fp32
+    ulp is ~3e-5, the regime the MUFU log-add-exp of the scans has to survive; ends through end_detect."""
+    nbest, ref = _case(25, 374, 800, 10, 28, dict(decoder=0.7, ctc=0.3, lm=0.4, length_bonus=0.5), True)
+    _check(nbest, ref, n_min=5)
+
+
 def test_pre_beam_key_on_one_scorer():
     nbest, ref = _case(24, 50, 3000, 6, 6, dict(decoder=0.7, ctc=0.3, lm=0.4), True, key="decoder")
     _check(nbest, ref)
