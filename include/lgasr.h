@@ -122,6 +122,14 @@ int lgasr_poll(lgasr_handle* h, int32_t* h_n_running, int32_t* h_done, int32_t* 
 int lgasr_gather_ended(lgasr_handle* h, int utt, int32_t* n_ended, int32_t* max_len, int64_t* h_tokens,
                        int32_t* h_lens, float* h_score, float* h_scores, void* stream);
 
+/* The best ended hypothesis of EVERY utterance in one call = head of the sorted n-best of BeamSearch.forward
+ * (beam_search.py:452-459; score, or score / (len - 1) with normalize_length; the first of equal scores, as
+ * Python's stable sort keeps it).  h_tokens [B][max_len] int64 padded with -1 (max_len >= primer_len +
+ * max_len_cap + 1), h_lens[B] (0: no hypothesis ended), h_score[B] (un-normalised).  Synchronises `stream`.
+ * This is the record an utterance-sharded driver gathers at the end. */
+int lgasr_gather_best(lgasr_handle* h, int normalize_length, int max_len, int64_t* h_tokens, int32_t* h_lens,
+                      float* h_score, void* stream);
+
 /* Per-kernel device timing (bench.py "roofline"): when on, every step records CUDA events around
  * its two kernels on the launching stream. lgasr_get_profile synchronises the events and returns
  * the accumulated durations (ms) since profiling was switched on, and the number of steps. */

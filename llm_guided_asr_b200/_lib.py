@@ -55,6 +55,7 @@ PROTOTYPES = {
     "lgasr_view": (_I, [_P, _I, C.POINTER(_P), C.POINTER(_I64)]),
     "lgasr_poll": (_I, [_P, _PI32, _PI32, _PI32, _PI32, _PI32, _P]),
     "lgasr_gather_ended": (_I, [_P, _I, _PI32, _PI32, _PI64, _PI32, _PF, _PF, _P]),
+    "lgasr_gather_best": (_I, [_P, _I, _I, _PI64, _PI32, _PF, _P]),
     "lgasr_launch_info": (_I, [_P, _PI32, _PI32, _PI32, _PI32]),
     "lgasr_set_profiling": (_I, [_P, _I]),
     "lgasr_get_profile": (_I, [_P, _PF, _PF, _PI32]),

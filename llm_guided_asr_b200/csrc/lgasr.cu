@@ -710,6 +710,50 @@ extern "C" int lgasr_gather_ended(lgasr_handle* h, int utt, int32_t* n_ended, in
   return LGASR_OK;
 }
 
+extern "C" int lgasr_gather_best(lgasr_handle* h, int normalize_length, int max_len, int64_t* h_tokens, int32_t* h_lens,
+                                 float* h_score, void* stream) {
+  if (!h || !h_tokens || !h_lens || !h_score) return fail(LGASR_EINVAL, "null argument");
+  Dev& d = h->d;
+  if (!h->begun) return fail(LGASR_ESTATE, "gather before begin");
+  if (!h->cache_valid) TRY(refresh_cache(h, (cudaStream_t)stream));
+  const int mx = h->cache_max_n, steps = h->cache_steps;
+  const int P = h->cfg.primer_len;
+  for (int utt = 0; utt < d.B; ++utt) {
+    const int n = h->c_n_ended[utt];
+    int64_t* row = h_tokens + (size_t)utt * max_len;
+    for (int t = 0; t < max_len; ++t) row[t] = -1;
+    int best = -1;
+    double bkey = 0.0;
+    for (int e = 0; e < n; ++e) {
+      const int4 m = h->c_meta[(size_t)utt * mx + e];
+      const float sc = h->c_score[(size_t)utt * mx + e];
+      // beam_search.py:452-459: python floats (double) of the fp32 score, / (len(yseq) - 1) when normalising
+      const double key = normalize_length ? (double)sc / (double)(m.z - 1) : (double)sc;
+      if (best < 0 || key > bkey) {
+        best = e;
+        bkey = key;
+      }
+    }
+    h_lens[utt] = 0;
+    h_score[utt] = 0.f;
+    if (best < 0) continue;
+    const int4 m = h->c_meta[(size_t)utt * mx + best];  // step, slot, len, extra_eos
+    if (m.z > max_len) return fail(LGASR_EINVAL, "max_len %d < hypothesis length %d", max_len, m.z);
+    for (int t = 0; t < P; ++t) row[t] = h->primer[t];
+    int slot = m.y;
+    for (int s2 = m.x; s2 >= 0; --s2) {
+      if (slot < 0) return fail(LGASR_ESTATE, "broken back-pointer chain (utt %d, ended %d)", utt, best);
+      const size_t o = ((size_t)utt * steps + s2) * d.W + slot;
+      row[P + s2] = h->c_bp_tok[o];
+      slot = h->c_bp_par[o];
+    }
+    if (m.w) row[P + m.x + 1] = d.eos;
+    h_lens[utt] = m.z;
+    h_score[utt] = h->c_score[(size_t)utt * mx + best];
+  }
+  return LGASR_OK;
+}
+
 extern "C" int lgasr_decode_replay(lgasr_handle* h, int n_steps, const float* const* h_term_ptr, const float* h_term_const,
                                    const float* h_term_weight, int64_t ld, void* stream) {
   if (!h) return fail(LGASR_EINVAL, "null handle");

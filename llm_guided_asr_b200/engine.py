@@ -179,6 +179,23 @@ class FusedStepEngine:
                 )
             )
 
+    def gather_best(self, normalize_length: bool = False):
+        """Best ended hypothesis of every utterance in one call (``lgasr_gather_best``): list of
+        ``(tokens, score)``; ``([], 0.0)`` where nothing ended."""
+        B = self.cfg.n_utts
+        ml = self.cfg.primer_len + self.cfg.max_len_cap + 1
+        toks = np.empty((B, ml), dtype=np.int64)
+        lens = np.empty(B, dtype=np.int32)
+        score = np.empty(B, dtype=np.float32)
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.lgasr_gather_best(
+                    self._h, 1 if normalize_length else 0, ml, toks.ctypes.data_as(_lib._PI64), lens.ctypes.data_as(_lib._PI32),
+                    score.ctypes.data_as(_lib._PF), _stream_ptr(self.device),
+                )
+            )
+        return [(toks[b, : lens[b]].tolist(), float(score[b])) for b in range(B)]
+
     def launch_info(self) -> dict:
         """Geometry of the fused step kernel of this handle (``lgasr_launch_info``)."""
         v = [C.c_int32() for _ in range(4)]

@@ -151,6 +151,11 @@ def _replay_host_equals_stepping():
         eng.step([d_tab[i]], [0.0], [0.7])
         eng.poll(with_parents=False)
     stepped = collect()
+    # lgasr_gather_best == the first maximum of gather_ended, for every utterance
+    best = eng.gather_best()
+    for b, (toks, score) in enumerate(stepped):
+        j = int(np.argmax(np.asarray(score, dtype=np.float32)))
+        assert best[b][0] == toks[j] and best[b][1] == np.float32(score[j])
     for _ in range(2):  # second pass replays the cached graph
         eng.set_posteriors(d_logp, lens)
         eng.begin(mx, mn, [eos])
