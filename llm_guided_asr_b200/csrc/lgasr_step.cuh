@@ -324,6 +324,20 @@ __device__ __forceinline__ void issue_cand_rows(const Dev& d, const unsigned lon
   const int Tp = d.Tp;
   const uint32_t rb = (uint32_t)Tp * 4u;
   fence_proxy_async();
+  if (g1 - g0 <= 2 * kStepWarps) {
+    // one candidate per lane: lanes w and w + 8 feed the barrier of consuming warp w
+    const int i = g0 + lane;
+    int cc = -1;
+    if (lane < 2 * kStepWarps && i < g1) cc = key_idx(keys[i]);
+    const bool need = cc >= 0 && cc != d.eos && !(d.eos != d.blank && cc == d.blank);
+    const uint32_t mine = need ? rb : 0u;
+    const uint32_t both = mine + __shfl_xor_sync(FULLMASK, mine, kStepWarps);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(&S->bar_cand[lane & (kStepWarps - 1)]);
+    if (lane < kStepWarps) mbar_expect_tx(bar, both);
+    __syncwarp();
+    if (need) bulk_g2s(arena + (long long)(i - g0) * Tp, xT_b + (long long)cc * Tp, rb, bar);
+    return;
+  }
   if (lane < kStepWarps) {
     uint32_t bytes = 0;
     for (int i = g0 + lane; i < g1; i += kStepWarps) {

@@ -49,3 +49,8 @@ print(f"select CTAs: n={last.sum()} ticket->loaded {d(12, 6):.0f}  loaded->ranke
 g0, g1 = tr[:, 0, 14], tr[:, 0, 15]
 print(f"globaltimer: CTA starts spread {(g0.max() - g0.min()) / 1e3:.2f} us; first start -> last end {(g1.max() - g0.min()) / 1e3:.2f} us; "
       f"median CTA life {np.median(g1 - g0) / 1e3:.2f} us; last ticket-CTA end - first start: {(g1[~last].max() - g0.min()) / 1e3:.2f} us")
+
+jd = tr[:, 0, 3] - np.maximum(tr[:, 0, 2], tr[:, 1, 2])
+print(f"join + state write-out after the later of (ctc_done, sel_done): median {np.median(jd):.0f} p90 {np.percentile(jd, 90):.0f} cycles; "
+      f"ctc later than sel in {np.mean(tr[:, 0, 2] > tr[:, 1, 2]) * 100:.0f}% of CTAs; cand_in - joined median {np.median(tr[:, 0, 4] - tr[:, 0, 3]):.0f}; "
+      f"cand_in - sel_done median {np.median(tr[:, 0, 4] - tr[:, 1, 2]):.0f}")
