@@ -189,6 +189,33 @@ int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blank, int m, c
 int lgasr_ctc_extend_state(const float* d_xT, int T_old, int T_new, int Tp_old, int Tp_new, int blank, int n,
                            const float* d_r_old, float* d_r_new, void* stream);
 
+/* ---- either side of the step ---------------------------------------------- */
+
+/* Re-order a caller-owned per-hypothesis cache of a full scorer (decoder / LM / LLM key-value or layer
+ * output cache) by the parents chosen at the LAST lgasr_step, reading them where the step left them on
+ * the device: no lgasr_poll / host round trip is needed before the next scorer call.  Replaces
+ * BatchBeamSearch.search's select_state per survivor (espnet/nets/batch_beam_search.py:347-355) and the
+ * per-layer torch.stack / unstack of BaseTransformerDecoder.batch_score
+ * (espnet2/asr/decoder/transformer_decoder.py:268-272,285-286).
+ *   d_src, d_dst: [n_outer][B*beam][row stride] bytes (outer = layer; strides may differ: the source may
+ *   be the tightly packed tensor a decoder just produced, the destination a padded persistent buffer);
+ *   dst[o][b*beam + j][0:row_bytes) = src[o][b*beam + parent[b][j]][0:row_bytes) for j < n_running[b];
+ *   other destination rows are left untouched.  row_bytes % 4 == 0; 16-byte accesses are used when every
+ *   pointer / stride / size allows.  d_dst != d_src (ping-pong buffers).  No-op before the first step. */
+int lgasr_reorder_rows(lgasr_handle* h, void* d_dst, const void* d_src, int64_t n_outer, int64_t dst_outer_bytes,
+                       int64_t src_outer_bytes, int64_t dst_row_bytes, int64_t src_row_bytes, int64_t row_bytes,
+                       void* stream);
+
+#define LGASR_F32 0
+#define LGASR_BF16 1
+/* d_out[r][0:vocab) = log_softmax(d_logits[r][0:vocab)) in fp32 for `rows` rows; d_logits fp32 (LGASR_F32)
+ * or bf16 (LGASR_BF16) with leading dimension ld_in elements, d_out fp32 with leading dimension ld_out:
+ * the (n, V) hand-off of the full scorers (torch.log_softmax at transformer_decoder.py:212,
+ * espnet2/asr/llm/llama.py:260,352) written straight into the padded row layout lgasr_step reads.
+ * vocab <= 131072 (rows above 16 K entries are split over a thread-block cluster of up to 8 CTAs). */
+int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t ld_in, float* d_out, int64_t ld_out, int rows,
+                           int vocab, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,8 @@ PROTOTYPES = {
     "lgasr_ctc_prefix_score": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P, _I, _P, _P, _P]),
     "lgasr_ctc_extend_state": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "lgasr_ctc_select_state": (_I, [_P, _I, _I, _I, _I, _P, _P, _P, _P, _I, _P, _P]),
+    "lgasr_reorder_rows": (_I, [_P, _P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _P]),
+    "lgasr_log_softmax_rows": (_I, [_P, _I, _I64, _P, _I64, _I, _I, _P]),
 }
 
 _lib = None

@@ -193,7 +193,11 @@ class BatchBeamSearch(torch.nn.Module):
         names = list(self.full_scorers)
         wts = [float(self.weights[k]) for k in names]
         # per-utterance scorer state lists (init_hyp, batch_beam_search.py:142-144)
-        states = {k: [[self.full_scorers[k].batch_init_state(x)] for x in xs] for k in names}
+        padded = {k for k in names if hasattr(self.full_scorers[k], "batch_score_padded")}
+        states = {k: [[self.full_scorers[k].batch_init_state(x)] for x in xs] for k in names if k not in padded}
+        for k in names:  # scorers that keep their per-hypothesis state on the device (device_cache.py)
+            if hasattr(self.full_scorers[k], "device_begin"):
+                self.full_scorers[k].device_begin(xs, lens, eng, len(primer) + max(maxlen))
         n_run = [1] * B
         done = [0] * B
         pad = {k: None for k in names}
@@ -249,9 +253,14 @@ class BatchBeamSearch(torch.nn.Module):
                     consts.append(0.0)
             eng.step(mats, consts, wts)
             steps += 1
-            nrun_new, done_new, par, _tok, n_active = eng.poll(with_parents=True)
+            for k in names:  # device-resident caches: parent-indexed gather queued behind the step
+                if hasattr(self.full_scorers[k], "device_reorder"):
+                    self.full_scorers[k].device_reorder()
+            nrun_new, done_new, par, _tok, n_active = eng.poll(with_parents=len(padded) < len(names))
             # re-order the full scorers' states by the parent slots (batch_beam_search.py:347-351)
             for k in names:
+                if k in padded:
+                    continue
                 d = self.full_scorers[k]
                 for b in range(B):
                     if done[b]:

@@ -14,6 +14,7 @@
 #include "lgasr_kernels.cuh"
 #include "lgasr_scorer_kernels.cuh"
 #include "lgasr_step.cuh"
+#include "lgasr_state_kernels.cuh"
 
 using namespace lgasr;
 
@@ -971,4 +972,92 @@ extern "C" int lgasr_ctc_extend_state(const float* d_xT, int T_old, int T_new, i
   k_ctc_extend_state<<<n, 128, smem, (cudaStream_t)stream>>>(d_xT, T_old, T_new, Tp_old, Tp_new, blank, d_r_old, d_r_new);
   LAUNCH_CK();
   return LGASR_OK;
+}
+
+// ---- either side of the step: scorer caches by parent, logits -> log-probabilities --------------------------
+extern "C" int lgasr_reorder_rows(lgasr_handle* h, void* d_dst, const void* d_src, int64_t n_outer, int64_t dst_outer_bytes,
+                                  int64_t src_outer_bytes, int64_t dst_row_bytes, int64_t src_row_bytes, int64_t row_bytes,
+                                  void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  if (!d_dst || !d_src || n_outer < 1 || n_outer > 65535 || row_bytes < 0 || dst_row_bytes < row_bytes ||
+      src_row_bytes < row_bytes || (row_bytes & 3))
+    return fail(LGASR_EINVAL, "bad argument");
+  if (d_dst == d_src) return fail(LGASR_EINVAL, "in-place reorder is not possible: use two buffers");
+  if (row_bytes == 0 || h->step == 0) return LGASR_OK;
+  Dev& d = h->d;
+  const int BW = d.B * d.W;
+  if (BW > 65535) return fail(LGASR_EINVAL, "too many rows");
+  const unsigned long long all = (unsigned long long)(uintptr_t)d_dst | (unsigned long long)(uintptr_t)d_src |
+                                 (unsigned long long)dst_outer_bytes | (unsigned long long)src_outer_bytes |
+                                 (unsigned long long)dst_row_bytes | (unsigned long long)src_row_bytes |
+                                 (unsigned long long)row_bytes;
+  const bool v16 = (all & 15) == 0;
+  const long long nvec = row_bytes / (v16 ? 16 : 4);
+  long long gx = (nvec + (long long)kCopyThreads * kCopyUnroll * 2 - 1) / ((long long)kCopyThreads * kCopyUnroll * 2);
+  if (gx < 1) gx = 1;
+  if (gx > 1024) gx = 1024;
+  dim3 grid((unsigned)gx, (unsigned)BW, (unsigned)n_outer);
+  cudaStream_t st = (cudaStream_t)stream;
+  // the parents of the last step and the running counts it produced (what lgasr_poll would copy out)
+  if (v16)
+    k_reorder_rows<uint4><<<grid, kCopyThreads, 0, st>>>(d.step_parent, d.n_run[h->pp], d.W, (char*)d_dst, (const char*)d_src,
+                                                         dst_outer_bytes, src_outer_bytes, dst_row_bytes, src_row_bytes,
+                                                         row_bytes);
+  else
+    k_reorder_rows<unsigned><<<grid, kCopyThreads, 0, st>>>(d.step_parent, d.n_run[h->pp], d.W, (char*)d_dst,
+                                                            (const char*)d_src, dst_outer_bytes, src_outer_bytes,
+                                                            dst_row_bytes, src_row_bytes, row_bytes);
+  LAUNCH_CK();
+  return LGASR_OK;
+}
+
+template <bool BF16, bool VECIO>
+static int launch_lsm(const void* logits, long long ld_in, float* out, long long ld_out, int rows, int V, int SL, int CS,
+                      cudaStream_t st) {
+  auto kern = k_log_softmax_rows<BF16, VECIO>;
+  const size_t smem = (size_t)SL * sizeof(float);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)CS, (unsigned)rows, 1);
+  cfg.blockDim = dim3(kLsmThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)CS;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, logits, ld_in, out, ld_out, V, SL);
+  if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
+  g_launches.fetch_add(1);
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t ld_in, float* d_out, int64_t ld_out, int rows,
+                                      int vocab, void* stream) {
+  if (!d_logits || !d_out || rows < 0 || rows > 65535 || vocab < 1 || ld_in < vocab || ld_out < vocab ||
+      (dtype != LGASR_F32 && dtype != LGASR_BF16))
+    return fail(LGASR_EINVAL, "bad argument");
+  if (rows == 0) return LGASR_OK;
+  // slice of a row per CTA: at most 16 K floats (64 KB: three CTAs per SM) -> cluster of 1, 2, 4 or 8 CTAs
+  const int kSlice = 16 * 1024;
+  int CS = 1;
+  while (CS < 8 && (long long)CS * kSlice < vocab) CS <<= 1;
+  if ((long long)CS * kSlice < vocab) return fail(LGASR_EINVAL, "vocabulary above %d", 8 * kSlice);
+  int SL = (vocab + CS - 1) / CS;
+  SL = (SL + 7) & ~7;  // slices start on 32-byte boundaries of the fp32 row (16-byte of a bf16 row)
+  const bool bf = dtype == LGASR_BF16;
+  const int vq = bf ? 8 : 4;
+  const bool vec = (vocab % vq) == 0 && (ld_in % vq) == 0 && (ld_out % 4) == 0 && (((uintptr_t)d_logits) & 15) == 0 &&
+                   (((uintptr_t)d_out) & 15) == 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bf) return vec ? launch_lsm<true, true>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st)
+                     : launch_lsm<true, false>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st);
+  return vec ? launch_lsm<false, true>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st)
+             : launch_lsm<false, false>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st);
 }

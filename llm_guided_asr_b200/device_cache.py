@@ -1,0 +1,150 @@
+"""Full-scorer state kept on the device, next to the fused step.
+
+What the reference does around every decoder call, per decode position:
+
+* ``BaseTransformerDecoder.batch_score`` stacks the per-hypothesis, per-layer caches into batch tensors
+  (``espnet2/asr/decoder/transformer_decoder.py:268-272``), calls ``forward_one_step`` (``:169-217``, ending in
+  ``torch.log_softmax`` ``:212``) and un-stacks the new caches into Python lists again (``:285-286``);
+* ``BatchBeamSearch.search`` then picks each survivor's state with ``select_state`` from Python
+  (``espnet/nets/batch_beam_search.py:347-355``), after the parents have been copied to the host.
+
+Here the caches of all ``B*beam`` row slots live in two persistent device buffers per scorer and are
+re-ordered by ONE parent-indexed gather per layer (``lgasr_reorder_rows``) that reads the parents where
+``k_step`` wrote them; the logits go through ``lgasr_log_softmax_rows`` straight into the row layout
+``lgasr_step`` consumes.  The decoder network itself stays in torch (§8 a18).
+"""
+
+import ctypes as C
+from typing import Any, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from .scorer_interface import BatchScorerInterface
+
+
+def log_softmax_rows(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``log_softmax(logits, dim=-1)`` in fp32 for a ``(rows, V)`` fp32 or bf16 CUDA tensor (rows may be
+    strided), by ``lgasr_log_softmax_rows``.  ``out``: optional ``(rows, V)`` fp32 destination."""
+    if logits.device.type != "cuda":
+        raise RuntimeError("log_softmax_rows needs a CUDA tensor: there is no CPU fallback")
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        raise ValueError("log_softmax_rows: (rows, V) tensor with unit stride along V expected")
+    if logits.dtype == torch.float32:
+        dt = 0
+    elif logits.dtype == torch.bfloat16:
+        dt = 1
+    else:
+        raise ValueError("log_softmax_rows: fp32 or bf16 logits expected")
+    rows, V = logits.shape
+    if out is None:
+        out = torch.empty(rows, V, dtype=torch.float32, device=logits.device)
+    if out.shape != (rows, V) or out.dtype != torch.float32 or out.stride(1) != 1 or out.device != logits.device:
+        raise ValueError("log_softmax_rows: out must be a (rows, V) fp32 tensor on the same device")
+    lib = _lib.load()
+    with torch.cuda.device(logits.device):
+        st = int(torch.cuda.current_stream(logits.device).cuda_stream)
+        ld_in = logits.stride(0) if rows > 1 else V
+        ld_out = out.stride(0) if rows > 1 else V
+        _lib.check(lib.lgasr_log_softmax_rows(C.c_void_p(logits.data_ptr()), dt, ld_in, C.c_void_p(out.data_ptr()), ld_out,
+                                              rows, V, st))
+    return out
+
+
+class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
+    """Full scorer around an attention decoder with the reference's ``BaseTransformerDecoder`` surface
+    (``embed``, ``decoders``, ``after_norm``, ``normalize_before``, ``output_layer``; the layers follow the
+    ``layer(tgt, tgt_mask, memory, memory_mask, cache=c)`` contract of ``forward_one_step``, ``:195-203``).
+
+    Used by this package's ``BatchBeamSearch`` through the device protocol (``device_begin`` /
+    ``batch_score_padded`` / ``device_reorder``): all ``B*beam`` row slots are scored in one decoder call per
+    position and the caches never leave the device.  Through the plain ``batch_score`` / ``select_state``
+    protocol (e.g. under the reference's own search) it simply delegates to the wrapped decoder.
+    """
+
+    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True):
+        torch.nn.Module.__init__(self)
+        for name in ("embed", "decoders", "output_layer"):
+            if not hasattr(decoder, name):
+                raise TypeError(f"decoder has no attribute {name!r}: not a BaseTransformerDecoder-like module")
+        self.decoder = decoder
+        self.fused_log_softmax = fused_log_softmax
+        self._eng = None
+
+    # ---- plain scorer protocol: delegate ------------------------------------------------------------------
+    def batch_init_state(self, x):
+        return self.decoder.batch_init_state(x) if hasattr(self.decoder, "batch_init_state") else None
+
+    def select_state(self, state, i, new_id=None):
+        return self.decoder.select_state(state, i) if hasattr(self.decoder, "select_state") else state[i]
+
+    def score(self, ys, state, x):
+        return self.decoder.score(ys, state, x)
+
+    def batch_score(self, ys: torch.Tensor, states: List[Any], xs: torch.Tensor) -> Tuple[torch.Tensor, List[Any]]:
+        return self.decoder.batch_score(ys, states, xs)
+
+    # ---- device protocol ----------------------------------------------------------------------------------
+    def device_begin(self, xs: Sequence[torch.Tensor], lens: Sequence[int], engine, max_positions: int) -> None:
+        """Start a batch: ``xs[b] (T_b, D)`` encoder outputs; row slot ``b*beam + j`` attends to ``xs[b]``."""
+        B, W = engine.cfg.n_utts, engine.cfg.beam
+        dev = xs[0].device
+        T = max(int(t) for t in lens)
+        mem = xs[0].new_zeros(B, T, xs[0].shape[-1])
+        for b, x in enumerate(xs):
+            mem[b, : lens[b]] = x
+        self._memory = mem.repeat_interleave(W, dim=0)  # (B*W, T, D)
+        ar = torch.arange(T, device=dev)
+        mask = ar[None, :] < torch.as_tensor(list(lens), device=dev)[:, None]  # (B, T)
+        self._memory_mask = mask.repeat_interleave(W, dim=0).unsqueeze(1)  # (B*W, 1, T)
+        self._eng = engine
+        self._cap = int(max_positions)
+        self._buf = None  # [2] x (n_layers, B*W, cap, Dm), allocated on the first call (Dm known then)
+        self._pp = 0
+        self._new = None
+        self._out = torch.empty(B * W, engine.cfg.vocab, dtype=torch.float32, device=dev)
+        self._V = engine.cfg.vocab
+
+    def batch_score_padded(self, yseq: torch.Tensor, n_run, done) -> torch.Tensor:
+        """``yseq (B, W, L)`` int64 running prefixes (all row slots) -> ``(B*W, V)`` fp32 log-probabilities;
+        rows of slots that are not running hold values nobody reads."""
+        dec = self.decoder
+        B, W, L = yseq.shape
+        tgt = yseq.reshape(B * W, L).clamp(0, self._V - 1)  # idle slots may hold stale ids
+        tgt_mask = torch.ones(L, L, dtype=torch.bool, device=tgt.device).tril().unsqueeze(0)
+        nl = len(dec.decoders)
+        if self._buf is None or L == 1:
+            cache = [None] * nl
+        else:
+            cache = [self._buf[self._pp][i, :, : L - 1] for i in range(nl)]
+        x = dec.embed(tgt)
+        memory, memory_mask = self._memory, self._memory_mask
+        new = []
+        for c, layer in zip(cache, dec.decoders):
+            x, tgt_mask, memory, memory_mask = layer(x, tgt_mask, memory, memory_mask, cache=c)
+            new.append(x)
+        y = x[:, -1]
+        if getattr(dec, "normalize_before", False) and getattr(dec, "after_norm", None) is not None:
+            y = dec.after_norm(y)
+        logits = dec.output_layer(y)
+        self._new = new
+        if self.fused_log_softmax:
+            return log_softmax_rows(logits if logits.dtype in (torch.float32, torch.bfloat16) else logits.float(), self._out)
+        self._out.copy_(torch.log_softmax(logits.float(), dim=-1))
+        return self._out
+
+    def device_reorder(self) -> None:
+        """Queue, right behind ``engine.step``, the gather of every layer's cache rows by the parents the step
+        chose (``lgasr_reorder_rows``): afterwards slot ``j`` of utterance ``b`` holds its parent's history."""
+        new = self._new
+        if new is None:
+            return
+        L, Dm = new[0].shape[1], new[0].shape[2]
+        if self._buf is None:
+            nl, BW = len(new), new[0].shape[0]
+            self._buf = [torch.zeros(nl, BW, self._cap, Dm, dtype=new[0].dtype, device=new[0].device) for _ in range(2)]
+        dst = self._buf[self._pp ^ 1]
+        for i, src in enumerate(new):
+            self._eng.reorder_rows(dst[i], src.contiguous(), row_elems=L * Dm)
+        self._pp ^= 1
+        self._new = None

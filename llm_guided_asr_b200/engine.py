@@ -196,6 +196,42 @@ class FusedStepEngine:
             )
         return [(toks[b, : lens[b]].tolist(), float(score[b])) for b in range(B)]
 
+    def reorder_rows(self, dst: torch.Tensor, src: torch.Tensor, row_elems: Optional[int] = None):
+        """``dst[o, b*W + j, :n] = src[o, b*W + parent[b][j], :n]`` for the hypotheses that survived the last
+        ``step`` (``lgasr_reorder_rows``): parents and running counts are read on the device, so this can be
+        queued right behind ``step`` without a ``poll``.  ``src``/``dst``: ``(n_outer, B*W, ...)`` or
+        ``(B*W, ...)`` with contiguous rows (row and outer strides may differ between the two);
+        ``row_elems`` (default: a whole ``src`` row) limits the copy to the leading elements of each row."""
+        BW = self.cfg.n_utts * self.cfg.beam
+        if src.dim() >= 2 and src.shape[0] == BW and (dst.shape[0] == BW):
+            src, dst = src.unsqueeze(0), dst.unsqueeze(0)
+        if src.shape[1] != BW or dst.shape[1] != BW or src.shape[0] != dst.shape[0] or src.dtype != dst.dtype:
+            raise ValueError("reorder_rows: (n_outer, B*beam, ...) tensors of one dtype expected")
+        es = src.element_size()
+
+        def rows_contiguous(t):
+            want = 1
+            for k in range(t.dim() - 1, 1, -1):
+                if t.shape[k] != 1 and t.stride(k) != want:
+                    return False
+                want *= t.shape[k]
+            return t.stride(1) >= want or t.shape[1] == 1
+
+        if not rows_contiguous(src) or not rows_contiguous(dst):
+            raise ValueError("reorder_rows: the trailing dimensions of a row must be contiguous")
+        n_src = int(np.prod(src.shape[2:])) if src.dim() > 2 else 1
+        n_dst = int(np.prod(dst.shape[2:])) if dst.dim() > 2 else 1
+        n = n_src if row_elems is None else int(row_elems)
+        if n > n_src or n > n_dst:
+            raise ValueError("reorder_rows: row_elems exceeds a row")
+        with torch.cuda.device(self.device):
+            _lib.check(
+                self.lib.lgasr_reorder_rows(
+                    self._h, C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr()), src.shape[0], dst.stride(0) * es,
+                    src.stride(0) * es, dst.stride(1) * es, src.stride(1) * es, n * es, _stream_ptr(self.device),
+                )
+            )
+
     def launch_info(self) -> dict:
         """Geometry of the fused step kernel of this handle (``lgasr_launch_info``)."""
         v = [C.c_int32() for _ in range(4)]

@@ -136,3 +136,82 @@ __all__ = [
     "random_table",
     "peaky_case",
 ]
+
+
+class _TinyDecoderLayer(torch.nn.Module):
+    """Pre-norm decoder layer with the call contract of the reference's ``DecoderLayer``
+    (``espnet/nets/pytorch_backend/transformer/decoder_layer.py``): ``layer(tgt, tgt_mask, memory,
+    memory_mask, cache=None) -> (x, tgt_mask, memory, memory_mask)``; with ``cache (n, L-1, D)`` only the
+    last position is computed and the result is ``cat([cache, x_last], dim=1)``."""
+
+    def __init__(self, D: int, heads: int, ff: int):
+        super().__init__()
+        self.H = heads
+        self.n1, self.n2, self.n3 = torch.nn.LayerNorm(D), torch.nn.LayerNorm(D), torch.nn.LayerNorm(D)
+        self.q1, self.kv1, self.o1 = torch.nn.Linear(D, D), torch.nn.Linear(D, 2 * D), torch.nn.Linear(D, D)
+        self.q2, self.kv2, self.o2 = torch.nn.Linear(D, D), torch.nn.Linear(D, 2 * D), torch.nn.Linear(D, D)
+        self.f1, self.f2 = torch.nn.Linear(D, ff), torch.nn.Linear(ff, D)
+
+    def _att(self, q, kv, mask):
+        n, Lq, D = q.shape
+        k, v = kv.chunk(2, dim=-1)
+        sp = lambda t: t.view(n, t.shape[1], self.H, D // self.H).transpose(1, 2)  # noqa: E731
+        a = torch.matmul(sp(q), sp(k).transpose(-1, -2)) / float(D // self.H) ** 0.5
+        if mask is not None:
+            a = a.masked_fill(~mask.unsqueeze(1), float("-inf"))
+        return torch.matmul(torch.softmax(a, dim=-1), sp(v)).transpose(1, 2).reshape(n, Lq, D)
+
+    def forward(self, tgt, tgt_mask, memory, memory_mask, cache=None):
+        y = self.n1(tgt)
+        if cache is None:
+            q_in, res, m1 = y, tgt, tgt_mask
+        else:
+            q_in, res = y[:, -1:], tgt[:, -1:]
+            m1 = None if tgt_mask is None else tgt_mask[:, -1:]
+        x = res + self.o1(self._att(self.q1(q_in), self.kv1(y), m1))
+        x = x + self.o2(self._att(self.q2(self.n2(x)), self.kv2(memory), memory_mask))
+        x = x + self.f2(torch.relu(self.f1(self.n3(x))))
+        if cache is not None:
+            x = torch.cat([cache, x], dim=1)
+        return x, tgt_mask, memory, memory_mask
+
+
+class TinyDecoder(torch.nn.Module, BatchScorerInterface):
+    """Small random-init attention decoder with the attribute and method surface of the reference's
+    ``BaseTransformerDecoder`` (``espnet2/asr/decoder/transformer_decoder.py:36-289``: ``embed``, ``decoders``,
+    ``after_norm``, ``normalize_before``, ``output_layer``, ``forward_one_step``, ``score``, ``batch_score`` with
+    per-hypothesis lists of per-layer ``(L, D)`` states).  Stands in for it on a box without the reference."""
+
+    def __init__(self, V: int, D: int = 32, layers: int = 2, heads: int = 4, ff: int = 64, seed: int = 0):
+        torch.nn.Module.__init__(self)
+        with torch.random.fork_rng(devices=[]):
+            torch.manual_seed(seed)
+            self.embed = torch.nn.Embedding(V, D)
+            self.decoders = torch.nn.ModuleList([_TinyDecoderLayer(D, heads, ff) for _ in range(layers)])
+            self.after_norm = torch.nn.LayerNorm(D)
+            self.output_layer = torch.nn.Linear(D, V)
+        self.normalize_before = True
+
+    def forward_one_step(self, tgt, tgt_mask, memory, memory_mask=None, *, cache=None):
+        x = self.embed(tgt)
+        if cache is None:
+            cache = [None] * len(self.decoders)
+        new_cache = []
+        for c, layer in zip(cache, self.decoders):
+            x, tgt_mask, memory, memory_mask = layer(x, tgt_mask, memory, memory_mask, cache=c)
+            new_cache.append(x)
+        y = self.after_norm(x[:, -1]) if self.normalize_before else x[:, -1]
+        return torch.log_softmax(self.output_layer(y), dim=-1), new_cache
+
+    def score(self, ys, state, x):
+        mask = torch.ones(ys.shape[0], ys.shape[0], dtype=torch.bool, device=ys.device).tril().unsqueeze(0)
+        logp, st = self.forward_one_step(ys.unsqueeze(0), mask, x.unsqueeze(0), cache=state)
+        return logp.squeeze(0), st
+
+    def batch_score(self, ys, states, xs):
+        n, L = ys.shape
+        nl = len(self.decoders)
+        cache = None if states[0] is None else [torch.stack([states[b][i] for b in range(n)]) for i in range(nl)]
+        mask = torch.ones(L, L, dtype=torch.bool, device=ys.device).tril().unsqueeze(0)
+        logp, st = self.forward_one_step(ys, mask, xs, cache=cache)
+        return logp, [[st[i][b] for i in range(nl)] for b in range(n)]

@@ -88,3 +88,24 @@ def test_scorer_partition_and_errors_mirror_reference():
     # CPU tensors are refused: there is no CPU fallback
     with pytest.raises(RuntimeError):
         bs(torch.zeros(5, V), 0.0, 0.0)
+
+
+def test_state_side_entry_points_validate_before_any_device_work():
+    # include/lgasr.h: lgasr_log_softmax_rows / lgasr_reorder_rows refuse bad arguments with LGASR_EINVAL
+    lib = _lib.load()
+    assert lib.lgasr_log_softmax_rows(None, 0, 10, None, 10, 1, 10, None) == -1
+    assert lib.lgasr_reorder_rows(None, None, None, 1, 0, 0, 0, 0, 0, None) == -1
+    from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer, log_softmax_rows
+
+    with pytest.raises(RuntimeError):
+        log_softmax_rows(torch.zeros(2, 8))  # CPU tensor: no fallback
+    with pytest.raises(TypeError):
+        DeviceCachedDecoderScorer(torch.nn.Linear(2, 2))
+    # the wrapper delegates the plain scorer protocol to the decoder it wraps
+    dec = syn.TinyDecoder(17, D=16, layers=1, heads=2, ff=16)
+    wrap = DeviceCachedDecoderScorer(dec)
+    ys = torch.tensor([[16, 3], [16, 5]])
+    mem = torch.randn(2, 6, 16)
+    a, _ = wrap.batch_score(ys, [None, None], mem)
+    b, _ = dec.batch_score(ys, [None, None], mem)
+    assert torch.equal(a, b)

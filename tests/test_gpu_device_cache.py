@@ -1,0 +1,160 @@
+"""GPU: the kernels either side of the fused step, through the C ABI.
+
+* ``lgasr_log_softmax_rows`` against ``torch.log_softmax`` in fp32 (tolerance 2e-5 abs: same formula, another
+  summation order), fp32 and bf16 logits, vocabularies from 30 to 128 256 (cluster of 8 CTAs per row), strided rows;
+* ``lgasr_reorder_rows`` bit-exact against ``index_select`` with the parents ``lgasr_poll`` reports, rows of idle
+  slots untouched, 16-byte and 4-byte paths, differing source / destination strides;
+* a decode with the decoder caches kept on the device (``DeviceCachedDecoderScorer``) against (i) the same search
+  with per-hypothesis host-side states (the reference's protocol) and (ii) the oracle search fed by a cache-free
+  full forward of the same decoder on the CPU: tokens equal, scores within 1e-4.
+"""
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import SCORE_ATOL
+from oracle.beam_search_oracle import BeamSearchOracle
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("V", [30, 1001, 5000, 16392, 50000, 128256])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_log_softmax_rows_matches_torch(V, dtype):
+    from llm_guided_asr_b200.device_cache import log_softmax_rows
+
+    g = torch.Generator().manual_seed(V)
+    rows = 13
+    x = (4.0 * torch.randn(rows, V, generator=g)).to(dtype).to(DEV)
+    x[3, V // 2] = 40.0  # a dominant entry
+    x[5] = -3.25  # a constant row
+    want = torch.log_softmax(x.float(), dim=-1)
+    got = log_softmax_rows(x)
+    assert got.dtype == torch.float32 and got.shape == (rows, V)
+    assert float((got - want).abs().max()) <= 2e-5
+    assert float((torch.logsumexp(got, dim=-1)).abs().max()) <= 2e-5
+
+
+def test_log_softmax_rows_strided_input_and_output():
+    from llm_guided_asr_b200.device_cache import log_softmax_rows
+
+    g = torch.Generator().manual_seed(5)
+    big = torch.randn(9, 1300, generator=g).to(DEV)
+    x = big[:, 3:1203]  # unaligned start, ld 1300
+    out_big = torch.full((9, 1400), 7.0, device=DEV)
+    out = out_big[:, :1200]
+    log_softmax_rows(x, out)
+    assert float((out - torch.log_softmax(x, dim=-1)).abs().max()) <= 2e-5
+    assert bool((out_big[:, 1200:] == 7.0).all())
+
+
+def _stepped_engine(B, W, V, seed=0):
+    from llm_guided_asr_b200.engine import FusedStepEngine
+    from llm_guided_asr_b200 import synthetic as syn
+
+    T, L = 40, 6
+    eos = V - 1
+    eng = FusedStepEngine(B, T, V, W, int(1.5 * W), ["decoder"], "full", True, 0.3, eos, eos, L, 1, False, device=torch.device(DEV))
+    logp = torch.stack([syn.random_logp(seed + b, T, V) for b in range(B)]).to(DEV)
+    eng.set_posteriors(logp, [T] * B)
+    eng.begin([L] * B, [0] * B, [eos])
+    g = torch.Generator().manual_seed(seed)
+    for i in range(3):
+        eng.step([torch.log_softmax(2 * torch.randn(B * W, V, generator=g), -1).to(DEV)], [0.0], [0.7])
+    return eng
+
+
+@pytest.mark.parametrize("elem,width", [(torch.float32, 64), (torch.float32, 3), (torch.bfloat16, 40), (torch.float32, 4096)])
+def test_reorder_rows_equals_index_select(elem, width):
+    B, W, V = 5, 4, 300
+    eng = _stepped_engine(B, W, V)
+    nrun, done, par, _tok, _ = eng.poll(with_parents=True)
+    nl, cap, L = 3, 9, 5
+    g = torch.Generator().manual_seed(1)
+    src = torch.randn(nl, B * W, L, width, generator=g).to(elem).to(DEV)
+    dst = torch.full((nl, B * W, cap, width), -1.0, dtype=elem, device=DEV)
+    eng.reorder_rows(dst, src, row_elems=L * width)
+    want = torch.full_like(dst, -1.0)
+    for b in range(B):
+        for j in range(int(nrun[b])):
+            want[:, b * W + j, :L] = src[:, b * W + int(par[b, j])]
+    assert torch.equal(dst, want)
+    assert int(nrun.sum()) > 0
+    # single-layer form, partial rows
+    dst2 = torch.zeros(B * W, cap, width, dtype=elem, device=DEV)
+    if (2 * width * src.element_size()) % 4 == 0:
+        eng.reorder_rows(dst2, src[1], row_elems=2 * width)
+        want2 = torch.zeros_like(dst2)
+        for b in range(B):
+            for j in range(int(nrun[b])):
+                want2[b * W + j, :2] = src[1, b * W + int(par[b, j]), :2]
+        assert torch.equal(dst2, want2)
+    with pytest.raises(RuntimeError):
+        eng.reorder_rows(src, src)
+    eng.close()
+
+
+def _full_forward_fn(dec, memory):
+    """Oracle full scorer: cache-free forward of the decoder over the whole prefix, CPU."""
+
+    def fn(ys):
+        ys = torch.as_tensor(np.asarray(ys))
+        n, L = ys.shape
+        mask = torch.ones(L, L, dtype=torch.bool).tril().unsqueeze(0)
+        with torch.no_grad():
+            logp, _ = dec.forward_one_step(ys, mask, memory.unsqueeze(0).expand(n, *memory.shape), cache=None)
+        return logp.numpy()
+
+    return fn
+
+
+@pytest.mark.parametrize("fused_lsm", [True, False])
+def test_device_cached_decoder_decode(fused_lsm):
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer, LengthBonus
+    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer
+
+    V, D, beam = 120, 32, 4
+    eos = V - 1
+    lens = [37, 52, 29]
+    g = torch.Generator().manual_seed(11)
+    encs = [torch.randn(t, D, generator=g) for t in lens]
+
+    class ProjCTC(torch.nn.Module):  # CTC head: linear + log_softmax (espnet2/asr/ctc.py:196-204)
+        def __init__(self):
+            super().__init__()
+            with torch.random.fork_rng(devices=[]):
+                torch.manual_seed(3)
+                self.lo = torch.nn.Linear(D, V)
+
+        def log_softmax(self, hs):
+            return torch.log_softmax(3.0 * self.lo(hs), dim=-1)
+
+    dec_cpu = syn.TinyDecoder(V, D=D, seed=2).eval()
+    ctc_cpu = ProjCTC().eval()
+    dec, ctc = syn.TinyDecoder(V, D=D, seed=2).eval().to(DEV), ProjCTC().eval().to(DEV)
+    weights = dict(decoder=0.7, ctc=0.3, length_bonus=0.3)
+
+    def search(decoder_scorer):
+        return BatchBeamSearch(scorers=dict(decoder=decoder_scorer, ctc=CTCPrefixScorer(ctc=ctc, eos=eos), length_bonus=LengthBonus(V)),
+                               weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
+
+    xs = [e.to(DEV) for e in encs]
+    got = search(DeviceCachedDecoderScorer(dec, fused_log_softmax=fused_lsm)).decode_batch(xs, -14, 0.0)
+    host = search(dec).decode_batch(xs, -14, 0.0)  # per-hypothesis host states (the reference's protocol)
+    for b in range(len(lens)):
+        assert len(got[b]) == len(host[b]) >= 1
+        for h, r in zip(got[b], host[b]):
+            assert h.yseq.tolist() == r.yseq.tolist()
+            assert abs(float(h.score) - float(r.score)) <= SCORE_ATOL
+        with torch.no_grad():
+            logp = ctc_cpu.log_softmax(encs[b].unsqueeze(0))[0].numpy()
+        full = dict(decoder=_full_forward_fn(dec_cpu, encs[b]), length_bonus=lambda ys: np.ones((len(ys), V), dtype=np.float32))
+        ref = BeamSearchOracle(full, weights, beam, V, eos, eos, pre_beam_score_key="full").forward(logp, -14, 0.0)
+        assert len(ref) == len(got[b])
+        for h, r in zip(got[b], ref):
+            assert h.yseq.tolist() == r.yseq
+            assert abs(float(h.score) - float(r.score)) <= SCORE_ATOL

@@ -88,6 +88,13 @@ def test_long_peaky_utterance_full_length():
     _check(nbest, ref, n_min=5)
 
 
+def test_owsm_shape_vocab_50000_two_matrices():
+    """configs[3] shape: T = 749 frames, V = 50 000, beam 5 (pre-beam 7), decoder + LM matrices: rows of
+    200 KB stream through the two-stage ring in many chunks; 3 KB state/posterior rows."""
+    nbest, ref = _case(26, 749, 50000, 5, 8, dict(decoder=0.7, ctc=0.3, lm=0.5), True, maxr=-10)
+    _check(nbest, ref)
+
+
 def test_pre_beam_key_on_one_scorer():
     nbest, ref = _case(24, 50, 3000, 6, 6, dict(decoder=0.7, ctc=0.3, lm=0.4), True, key="decoder")
     _check(nbest, ref)
