@@ -1015,7 +1015,7 @@ template <bool BF16, bool VECIO>
 static int launch_lsm(const void* logits, long long ld_in, float* out, long long ld_out, int rows, int V, int SL, int CS,
                       cudaStream_t st) {
   auto kern = k_log_softmax_rows<BF16, VECIO>;
-  const size_t smem = (size_t)SL * sizeof(float);
+  const size_t smem = (size_t)SL * (BF16 ? 2 : 4);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));

@@ -72,14 +72,48 @@ __device__ __forceinline__ unsigned cluster_ctarank() {
   return r;
 }
 
+constexpr int kLsmChunks = 4;  // TMA chunks per slice (separate mbarriers: the maximum pass starts on chunk 0)
+
+template <bool BF16>
+struct LsmIn {
+  using T = float;
+  static constexpr int kVec = 4;  // elements per 16 bytes
+  __device__ static __forceinline__ float at(const T* p, int i) { return p[i]; }
+  __device__ static __forceinline__ void vec(const T* p, int i, float* f) {
+    const float4 q = reinterpret_cast<const float4*>(p)[i];
+    f[0] = q.x, f[1] = q.y, f[2] = q.z, f[3] = q.w;
+  }
+};
+template <>
+struct LsmIn<true> {
+  using T = __nv_bfloat16;
+  static constexpr int kVec = 8;
+  __device__ static __forceinline__ float at(const T* p, int i) { return __bfloat162float(p[i]); }
+  __device__ static __forceinline__ void vec(const T* p, int i, float* f) {
+    const uint4 q = reinterpret_cast<const uint4*>(p)[i];
+    const unsigned w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {  // bf16 -> fp32 is a 16-bit shift
+      f[2 * k] = __uint_as_float(w[k] << 16);
+      f[2 * k + 1] = __uint_as_float(w[k] & 0xffff0000u);
+    }
+  }
+};
+
 // out[r][v] = x[r][v] - (m + log(sum_v exp(x[r][v] - m))), m = max_v x[r][v], all in fp32.
 // One row per cluster (gridDim.x = cluster size CS along x, blockIdx.y = row); CTA c owns the contiguous
-// slice [c*SL, min(V, (c+1)*SL)) staged in dynamic shared memory (SL floats).  BF16: logits are bf16.
-// VECIO: V, SL, both leading dimensions and both pointers allow 16-byte accesses.
+// slice [c*SL, min(V, (c+1)*SL)), staged ONCE in dynamic shared memory in its input type (SL elements).
+// BF16: logits are bf16.  VECIO: V, SL, both leading dimensions and both pointers allow 16-byte accesses;
+// the slice then arrives by kLsmChunks 1-D TMA bulk copies (cp.async.bulk + mbarrier), else by plain loads.
 template <bool BF16, bool VECIO>
 __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __restrict__ logits, long long ld_in,
                                                                   float* __restrict__ out, long long ld_out, int V, int SL) {
-  extern __shared__ __align__(16) float row_s[];
+  using In = LsmIn<BF16>;
+  using T = typename In::T;
+  constexpr int NV = In::kVec;
+  extern __shared__ __align__(16) unsigned char lsm_raw[];
+  T* row_s = reinterpret_cast<T*>(lsm_raw);
+  __shared__ __align__(8) unsigned long long bar[kLsmChunks];
   __shared__ float red[kLsmThreads / 32];
   __shared__ float xm[16], xs[16];  // (max, sum) of every CTA of the cluster, written by the peers
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -87,46 +121,43 @@ __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __
   const long long r = blockIdx.y;
   const int v0 = (int)c * SL;
   const int n = (V - v0 < SL) ? (V - v0 > 0 ? V - v0 : 0) : SL;
+  const T* x = reinterpret_cast<const T*>(logits) + r * ld_in + v0;
   if (CS > 1) cluster_arrive();  // phase 1: every CTA of the cluster runs (its xm/xs may be written)
 
-  // stage the slice as fp32, running maximum on the way
   float m = -INFINITY;
-  if (BF16) {
-    const __nv_bfloat16* x = reinterpret_cast<const __nv_bfloat16*>(logits) + r * ld_in + v0;
-    if (VECIO) {
-      const uint4* x8 = reinterpret_cast<const uint4*>(x);
-      for (int i = tid; i < (n >> 3); i += kLsmThreads) {
-        const uint4 q = __ldcs(x8 + i);
-        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&q.x));
-        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&q.y));
-        const float2 cc = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&q.z));
-        const float2 dd = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&q.w));
-        reinterpret_cast<float4*>(row_s)[2 * i] = make_float4(a.x, a.y, b.x, b.y);
-        reinterpret_cast<float4*>(row_s)[2 * i + 1] = make_float4(cc.x, cc.y, dd.x, dd.y);
-        m = fmaxf(m, fmaxf(fmaxf(fmaxf(a.x, a.y), fmaxf(b.x, b.y)), fmaxf(fmaxf(cc.x, cc.y), fmaxf(dd.x, dd.y))));
+  const int nv = n / NV;  // VECIO: n % NV == 0
+  // chunk k covers vectors [k*cv, min(nv, (k+1)*cv))
+  const int cv = (nv + kLsmChunks - 1) / kLsmChunks;
+  if (VECIO) {
+    if (tid == 0) {
+#pragma unroll
+      for (int k = 0; k < kLsmChunks; ++k) mbar_init(reinterpret_cast<uint64_t*>(&bar[k]), 1);
+      mbar_fence_init();
+#pragma unroll
+      for (int k = 0; k < kLsmChunks; ++k) {
+        const int a = k * cv, b = (a + cv < nv) ? a + cv : nv;
+        const uint32_t bytes = b > a ? (uint32_t)(b - a) * 16u : 0u;
+        mbar_expect_tx(reinterpret_cast<uint64_t*>(&bar[k]), bytes);
+        if (bytes) bulk_g2s(row_s + (long long)a * NV, x + (long long)a * NV, bytes, reinterpret_cast<uint64_t*>(&bar[k]));
       }
-    } else {
-      for (int i = tid; i < n; i += kLsmThreads) {
-        const float f = __bfloat162float(x[i]);
-        row_s[i] = f;
-        m = fmaxf(m, f);
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int k = 0; k < kLsmChunks; ++k) {
+      mbar_wait(reinterpret_cast<uint64_t*>(&bar[k]), 0);
+      const int a = k * cv, b = (a + cv < nv) ? a + cv : nv;
+      for (int i = a + tid; i < b; i += kLsmThreads) {
+        float f[NV];
+        In::vec(row_s, i, f);
+#pragma unroll
+        for (int e = 0; e < NV; ++e) m = fmaxf(m, f[e]);
       }
     }
   } else {
-    const float* x = reinterpret_cast<const float*>(logits) + r * ld_in + v0;
-    if (VECIO) {
-      const float4* x4 = reinterpret_cast<const float4*>(x);
-      for (int i = tid; i < (n >> 2); i += kLsmThreads) {
-        const float4 q = __ldcs(x4 + i);
-        reinterpret_cast<float4*>(row_s)[i] = q;
-        m = fmaxf(m, fmaxf(fmaxf(q.x, q.y), fmaxf(q.z, q.w)));
-      }
-    } else {
-      for (int i = tid; i < n; i += kLsmThreads) {
-        const float f = x[i];
-        row_s[i] = f;
-        m = fmaxf(m, f);
-      }
+    for (int i = tid; i < n; i += kLsmThreads) {
+      const T t = x[i];
+      row_s[i] = t;
+      m = fmaxf(m, In::at(&t, 0));
     }
   }
   m = warp_max(m);
@@ -136,16 +167,17 @@ __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __
 #pragma unroll
   for (int w = 1; w < kLsmThreads / 32; ++w) m = fmaxf(m, red[w]);
   __syncthreads();
-  // sum of exp(x - m) over the slice (each thread re-reads what it staged itself or its neighbours did:
-  // the barrier above orders the shared-memory writes)
+  // sum of exp(x - m) over the slice
   float s = 0.f;
   if (VECIO) {
-    for (int i = tid; i < (n >> 2); i += kLsmThreads) {
-      const float4 q = reinterpret_cast<const float4*>(row_s)[i];
-      s += (__expf(q.x - m) + __expf(q.y - m)) + (__expf(q.z - m) + __expf(q.w - m));
+    for (int i = tid; i < nv; i += kLsmThreads) {
+      float f[NV];
+      In::vec(row_s, i, f);
+#pragma unroll
+      for (int e = 0; e < NV; e += 2) s += __expf(f[e] - m) + __expf(f[e + 1] - m);
     }
   } else {
-    for (int i = tid; i < n; i += kLsmThreads) s += __expf(row_s[i] - m);
+    for (int i = tid; i < n; i += kLsmThreads) s += __expf(In::at(row_s, i) - m);
   }
   s = warp_sum(s);
   if (lane == 0) red[warp] = s;
@@ -170,19 +202,19 @@ __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __
     m = M;
     s = S;
   }
-  const float lse = m + __logf(s);
+  const float lse = m + logf(s);
   float* o = out + r * ld_out + v0;
   if (VECIO) {
-    for (int i = tid; i < (n >> 2); i += kLsmThreads) {
-      float4 q = reinterpret_cast<const float4*>(row_s)[i];
-      q.x -= lse;
-      q.y -= lse;
-      q.z -= lse;
-      q.w -= lse;
-      __stcs(reinterpret_cast<float4*>(o) + i, q);
+    for (int i = tid; i < nv; i += kLsmThreads) {
+      float f[NV];
+      In::vec(row_s, i, f);
+#pragma unroll
+      for (int e = 0; e < NV; e += 4)
+        __stcs(reinterpret_cast<float4*>(o) + (long long)i * (NV / 4) + e / 4,
+               make_float4(f[e] - lse, f[e + 1] - lse, f[e + 2] - lse, f[e + 3] - lse));
     }
   } else {
-    for (int i = tid; i < n; i += kLsmThreads) o[i] = row_s[i] - lse;
+    for (int i = tid; i < n; i += kLsmThreads) o[i] = In::at(row_s, i) - lse;
   }
 }
 
