@@ -216,6 +216,13 @@ int lgasr_reorder_rows(lgasr_handle* h, void* d_dst, const void* d_src, int64_t 
 int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t ld_in, float* d_out, int64_t ld_out, int rows,
                            int vocab, void* stream);
 
+/* Timestamp-rule full scorer of the OWSM recipe = ScoreFilter.batch_score
+ * (espnet2/bin/s2t_inference.py:47-146): d_out[r][0:vocab) = 0.0 or -inf from the prefix
+ * d_yseq[r][0:cur_len) (int64, leading dimension ld_y; e.g. the handle's yseq view).  Where the reference
+ * raises IndexError (cur_len < 3 without <notimestamps> in the prefix) y[-3] is taken as "not sos". */
+int lgasr_score_filter(const int64_t* d_yseq, int64_t ld_y, int cur_len, int rows, int vocab, int notimestamps,
+                       int first_time, int last_time, int sos, int eos, float* d_out, int64_t ld_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1061,3 +1061,18 @@ extern "C" int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t l
   return vec ? launch_lsm<false, true>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st)
              : launch_lsm<false, false>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st);
 }
+
+extern "C" int lgasr_score_filter(const int64_t* d_yseq, int64_t ld_y, int cur_len, int rows, int vocab, int notimestamps,
+                                  int first_time, int last_time, int sos, int eos, float* d_out, int64_t ld_out,
+                                  void* stream) {
+  if (!d_yseq || !d_out || rows < 0 || vocab < 1 || cur_len < 1 || ld_y < cur_len || ld_out < vocab || first_time < 0 ||
+      last_time < first_time || last_time >= vocab || eos < 0 || eos >= vocab)
+    return fail(LGASR_EINVAL, "bad argument");
+  if (rows == 0) return LGASR_OK;
+  const int vec_ok = (vocab % 4 == 0) && (ld_out % 4 == 0) && ((((uintptr_t)d_out) & 15) == 0);
+  k_score_filter<<<rows, kFilterThreads, 0, (cudaStream_t)stream>>>((const long long*)d_yseq, ld_y, cur_len, vocab,
+                                                                     notimestamps, first_time, last_time, sos, eos, d_out,
+                                                                     ld_out, vec_ok);
+  LAUNCH_CK();
+  return LGASR_OK;
+}

@@ -218,4 +218,69 @@ __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __
   }
 }
 
+// ---- timestamp-rule scorer of the OWSM recipe --------------------------------------------------------------
+// out[r][v] = 0 or -inf by the rules of ScoreFilter.score (espnet2/bin/s2t_inference.py:88-116) applied to the
+// prefix y = yseq[r][0:L).  One CTA per row: the prefix is reduced to five scalars (contains <notimestamps>,
+// number of timestamp tokens, the last timestamp, y[-1], y[-3]), then the row is written with 16-byte stores.
+// The reference evaluates the rules per hypothesis in Python (batch_score loops over score, :140-146).
+constexpr int kFilterThreads = 128;
+
+__global__ __launch_bounds__(kFilterThreads) void k_score_filter(const long long* __restrict__ yseq, long long ld_y, int L,
+                                                                 int V, int notime, int first, int last, int sos, int eos,
+                                                                 float* __restrict__ out, long long ld_out, int vec_ok) {
+  __shared__ int s_has, s_cnt, s_lastpos;
+  const int tid = threadIdx.x;
+  const long long* y = yseq + blockIdx.x * ld_y;
+  if (tid == 0) {
+    s_has = 0;
+    s_cnt = 0;
+    s_lastpos = -1;
+  }
+  __syncthreads();
+  int has = 0, cnt = 0, lastpos = -1;
+  for (int i = tid; i < L; i += kFilterThreads) {
+    const long long t = y[i];
+    has |= (t == notime);
+    if (t >= first && t <= last) {
+      ++cnt;
+      lastpos = i;
+    }
+  }
+  if (has) atomicOr(&s_has, 1);
+  if (cnt) {
+    atomicAdd(&s_cnt, cnt);
+    atomicMax(&s_lastpos, lastpos);
+  }
+  __syncthreads();
+  // rule -> (lo, hi, inside, eos_override): entry v is -inf iff ((lo <= v <= hi) == inside), except eos when
+  // eos_override is 0 (forced 0.0) or 1 (forced -inf)
+  int lo, hi, inside = 1, eos_ov = -1;
+  const long long y1 = L >= 1 ? y[L - 1] : -1, y3 = L >= 3 ? y[L - 3] : (long long)sos + 1;
+  if (s_has) {  // :93-95
+    lo = first, hi = last;
+  } else if (y3 == sos) {  // :96-99
+    lo = first, hi = last, inside = 0;
+  } else if (s_cnt & 1) {  // :102-106
+    lo = first, hi = (int)y[s_lastpos];
+    eos_ov = 1;
+  } else if (y1 >= first && y1 <= last) {  // :109-113
+    lo = (int)y1, hi = last, inside = 0;
+    eos_ov = 0;
+  } else {  // :114-116
+    lo = 0, hi = -1, inside = 0;
+  }
+  const float NEG = -INFINITY;
+  float* o = out + blockIdx.x * ld_out;
+  auto val = [&](int v) -> float {
+    if (v == eos && eos_ov >= 0) return eos_ov ? NEG : 0.f;
+    return ((v >= lo && v <= hi) == (inside != 0)) ? NEG : 0.f;
+  };
+  if (vec_ok) {
+    for (int i = tid; i < (V >> 2); i += kFilterThreads)
+      reinterpret_cast<float4*>(o)[i] = make_float4(val(4 * i), val(4 * i + 1), val(4 * i + 2), val(4 * i + 3));
+  } else {
+    for (int v = tid; v < V; v += kFilterThreads) o[v] = val(v);
+  }
+}
+
 }  // namespace lgasr

@@ -11,9 +11,12 @@ from llm_guided_asr_b200 import synthetic as syn
 from oracle.beam_search_oracle import BeamSearchOracle, torch_scorer_fn
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-# whole-search goldens (make_golden.py); streaming.npz (make_golden_streaming.py) has its own tests
+# whole-search goldens (make_golden.py); streaming.npz (make_golden_streaming.py) and score_filter.npz
+# (make_golden_score_filter.py) have their own tests
 GOLDEN_NAMES = sorted(
-    os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")) if os.path.basename(p) != "streaming.npz"
+    os.path.basename(p)[:-4]
+    for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz"))
+    if os.path.basename(p) not in ("streaming.npz", "score_filter.npz")
 )
 
 # fp32 score tolerance of BASELINE.json's north_star: 1e-4 absolute.

@@ -158,3 +158,68 @@ def test_device_cached_decoder_decode(fused_lsm):
         for h, r in zip(got[b], ref):
             assert h.yseq.tolist() == r.yseq
             assert abs(float(h.score) - float(r.score)) <= SCORE_ATOL
+
+
+def test_score_filter_matches_reference_goldens_and_oracle():
+    import os
+
+    from llm_guided_asr_b200.score_filter import ScoreFilter
+    from oracle.score_filter_oracle import score_filter
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "score_filter.npz"))
+    V, sos, eos, notime, first, last = [int(v) for v in g["spec"]]
+    f = ScoreFilter(notime, first, last, sos, eos, V).to(DEV)
+    for n in sorted(set(int(v) for v in g["lens"])):
+        idx = [i for i in range(len(g["ys"])) if g["lens"][i] == n]
+        ys = torch.as_tensor(g["ys"][idx, :n]).to(DEV)
+        out, st = f.batch_score(ys, [None] * len(idx), None)
+        out = out.cpu().numpy()
+        assert np.all((out == 0) | np.isneginf(out)) and st == [None] * len(idx)
+        assert np.array_equal(np.isneginf(out), g["masks"][idx])  # recorded from the reference class
+        one, _ = f.score(ys[0], None, None)
+        assert np.array_equal(np.isneginf(one.cpu().numpy()), g["masks"][idx[0]])
+    # a vocabulary that is not a multiple of 4 and a strided prefix array, against the oracle
+    V2 = 1003
+    f2 = ScoreFilter(3, 500, 999, 1, 2, V2).to(DEV)
+    rng = np.random.RandomState(4)
+    big = rng.randint(4, V2, size=(6, 5, 20)).astype(np.int64)
+    big[:, :, 0], big[:, :, 1], big[:, :, 2] = 1, 7, 8
+    big[0, :, 2] = 3
+    d_big = torch.as_tensor(big).to(DEV)
+    for L in (3, 4, 9, 20):
+        got = f2.batch_score_padded(d_big[:, :, :L], None, None).cpu().numpy()
+        want = score_filter(big[:, :, :L].reshape(30, L), V2, 1, 2, 3, 500, 999)
+        assert np.array_equal(got, want)
+
+
+def test_fused_search_with_score_filter_and_primer():
+    """OWSM-style decode: <sos><lang><task> primer, timestamp rules as an extra full scorer (weight 1.0) whose
+    -inf entries go through the fusion, the pre-beam and the final top-k; against the oracle search."""
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer
+    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.score_filter import ScoreFilter
+    from oracle.score_filter_oracle import score_filter
+
+    V, beam, T = 200, 5, 60
+    sos, eos, notime, first, last = 1, 2, 3, 100, 199
+    logp = syn.random_logp(9, T, V, scale=2.0)
+    table = syn.random_table(10, 64, 4, V, scale=1.5)
+    weights = dict(decoder=0.7, ctc=0.3, scorefilter=1.0)
+    primer = [sos, 5, 6]
+    for prim in (primer, [sos, 5, notime]):
+        bs = BatchBeamSearch(
+            scorers=dict(decoder=syn.PrefixTableScorer(table.to(DEV)), ctc=CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=eos),
+                         scorefilter=ScoreFilter(notime, first, last, sos, eos, V).to(DEV)),
+            weights=weights, beam_size=beam, vocab_size=V, sos=sos, eos=eos, pre_beam_score_key="full")
+        bs.set_hyp_primer(prim)
+        got = bs(logp.to(DEV), -12, 0.0)
+        from oracle.beam_search_oracle import torch_scorer_fn
+
+        full = dict(decoder=torch_scorer_fn(syn.PrefixTableScorer(table)),
+                    scorefilter=lambda ys: score_filter(np.asarray(ys), V, sos, eos, notime, first, last))
+        orc = BeamSearchOracle(full, weights, beam, V, sos, eos, pre_beam_score_key="full", hyp_primer=prim)
+        ref = orc.forward(logp.numpy(), -12, 0.0)
+        assert len(got) == len(ref) >= 1
+        for h, r in zip(got, ref):
+            assert h.yseq.tolist() == r.yseq
+            assert abs(float(h.score) - float(r.score)) <= SCORE_ATOL
