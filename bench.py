@@ -404,6 +404,12 @@ def main():
         return
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        from llm_guided_asr_b200.sharding import bind_to_gpu_numa
+
+        cpus = bind_to_gpu_numa(local_rank)  # pinned host buffers on the GPU's own socket (e2e leg)
+        if os.environ.get("LGASR_BENCH_VERBOSE"):
+            print(f"[bench] rank {rank}: bound to {len(cpus) if cpus else 0} cores "
+                  f"({cpus[0]}..{cpus[-1]})" if cpus else f"[bench] rank {rank}: not bound", file=sys.stderr)
         torch.cuda.set_device(local_rank)
         torch.distributed.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     try:

@@ -88,3 +88,39 @@ def shard_summary(lengths: Sequence[int], world: int) -> Dict[str, List[int]]:
     """Counts and frame sums per shard (imbalance report of the driver)."""
     sh = partition(lengths, world)
     return {"count": [len(s) for s in sh], "frames": [sum(int(lengths[i]) for i in s) for s in sh]}
+
+
+def bind_to_gpu_numa(device_index: int) -> Optional[List[int]]:
+    """Pin the calling process to the host cores NVML reports as local to GPU ``device_index`` BEFORE it
+    allocates pinned staging buffers, so that (first-touch) they land on the memory of the socket the GPU
+    hangs off: with one process per GPU all pulling host buffers at PCIe rate, cross-socket traffic is what
+    limits the host->device leg.  Returns the core list, or None when NVML / the cpuset does not allow it
+    (nothing is changed then)."""
+    import os
+
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = device_index
+        if vis:
+            ent = vis.split(",")[device_index].strip()
+            if ent.isdigit():
+                idx = int(ent)
+            else:
+                idx = None
+                h = pynvml.nvmlDeviceGetHandleByUUID(ent)
+        if idx is not None:
+            h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        n = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n + 63) // 64)
+        cpus = [64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus or len(cpus) == len(allowed):
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
