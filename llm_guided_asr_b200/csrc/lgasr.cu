@@ -284,17 +284,24 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     }
     static size_t cur_step = 0;
     if (e == cudaSuccess && h->fused && h->smem_step > cur_step) {
-      e = cudaFuncSetAttribute(k_step<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step);
+      const int sm = (int)h->smem_step;
+      e = cudaFuncSetAttribute(k_step<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
       if (e == cudaSuccess) cur_step = h->smem_step;
     }
     if (e == cudaSuccess && h->cluster) {
       static bool np_set = false;
       if (!np_set) {
-        e = cudaFuncSetAttribute(k_step<false, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        e = cudaFuncSetAttribute(k_step<false, true, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<false, true, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         np_set = (e == cudaSuccess);
       }
       // can at least one cluster of `beam` CTAs be resident?  otherwise fall back to the ticket variant
@@ -312,7 +319,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       qc.numAttrs = 1;
       // clusters only pay while every utterance's cluster is resident at once (one wave): with more utterances
       // than that, whole-cluster scheduling leaves CTA slots idle (measured: 113 vs 94 us per launch at B = 512)
-      if (e != cudaSuccess || cudaOccupancyMaxActiveClusters(&ncl_max, k_step<false, true>, &qc) != cudaSuccess ||
+      if (e != cudaSuccess || cudaOccupancyMaxActiveClusters(&ncl_max, k_step<false, true, false>, &qc) != cudaSuccess ||
           ncl_max < d.B) {
         cudaGetLastError();
         e = cudaSuccess;
@@ -496,7 +503,14 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
       at[na].val.programmaticStreamSerializationAllowed = 1;
       ++na;
     }
-    if (h->cluster) {
+    // SEQ variant (selection before griddepcontrol.wait, four CTC warps after it) for programmatic launches.
+    // It runs as single CTAs with the ticket hand-off: clusters of `beam` CTAs only become resident when ten
+    // slots of one GPC are free at once, which delays the early start the variant lives on (measured: 20.2 us
+    // per launch with clusters, 17.9 us without).
+    const char* nseq = getenv("LGASR_NO_SEQ");
+    const bool seq = pdl && !(nseq && nseq[0] == '1');
+    const bool use_cluster = h->cluster && !seq;
+    if (use_cluster) {
       at[na].id = cudaLaunchAttributeClusterDimension;
       at[na].val.clusterDim.x = d.W;
       at[na].val.clusterDim.y = 1;
@@ -506,17 +520,15 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     cfg.attrs = at;
     cfg.numAttrs = na;
     sl.pdl = pdl ? 1 : 0;
-    if (h->cluster) {
-      if (d.trace)
-        CK(cudaLaunchKernelEx(&cfg, k_step<true, true>, d, tm, sl, h->pp, h->rp, h->step));
-      else
-        CK(cudaLaunchKernelEx(&cfg, k_step<false, true>, d, tm, sl, h->pp, h->rp, h->step));
+    auto kern = k_step<false, false, false>;
+    if (use_cluster) {
+      if (d.trace) kern = seq ? k_step<true, true, true> : k_step<true, true, false>;
+      else kern = seq ? k_step<false, true, true> : k_step<false, true, false>;
     } else {
-      if (d.trace)
-        CK(cudaLaunchKernelEx(&cfg, k_step<true, false>, d, tm, sl, h->pp, h->rp, h->step));
-      else
-        CK(cudaLaunchKernelEx(&cfg, k_step<false, false>, d, tm, sl, h->pp, h->rp, h->step));
+      if (d.trace) kern = seq ? k_step<true, false, true> : k_step<true, false, false>;
+      else kern = seq ? k_step<false, false, true> : k_step<false, false, false>;
     }
+    CK(cudaLaunchKernelEx(&cfg, kern, d, tm, sl, h->pp, h->rp, h->step));
     LAUNCH_CK();
     if (h->profiling) {
       CK(cudaEventRecord(pe[1], st));
@@ -810,6 +822,7 @@ extern "C" int lgasr_decode_replay(lgasr_handle* h, int n_steps, const float* co
       return rc;
     }
     if (ee != cudaSuccess) return fail(LGASR_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ee));
+    if (const char* dot = getenv("LGASR_GRAPH_DOT")) cudaGraphDebugDotPrint(g, dot, cudaGraphDebugDotFlagsVerbose);
     const cudaError_t ei = cudaGraphInstantiate(&h->rg_exec, g, 0);
     cudaGraphDestroy(g);
     if (ei != cudaSuccess) {

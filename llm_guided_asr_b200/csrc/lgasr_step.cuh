@@ -101,12 +101,14 @@ __device__ __forceinline__ int key_idx(unsigned long long k) { return (int)(~(un
 // alias y).  g: thread index in the group; ws: 2*kCtcWarps floats of shared scratch.  Ends with a group
 // barrier.  Deliberately ONE out-of-line copy with rolled loops: the step kernel must stay small enough for
 // the instruction cache (straight-line code runs at fetch speed, not at issue speed).
+template <int NCW>
 __device__ __noinline__ void group_affine_scan(const float* a, const float* b, float* y, int start, int T, float y0, int g,
                                                float* ws, int bar_id) {
+  constexpr int NCT = 32 * NCW;
   const int n = T - start;
   if (n <= 0) return;  // group-uniform
   const int lane = g & 31, w = g >> 5;
-  int L = (n + kCtcThreads - 1) / kCtcThreads;
+  int L = (n + NCT - 1) / NCT;
   L |= 1;  // odd segment length: the lanes of a warp hit distinct banks
   int s0 = start + g * L;
   int s1 = s0 + L;
@@ -134,7 +136,7 @@ __device__ __noinline__ void group_affine_scan(const float* a, const float* b, f
   }
   if (lane == 31) {
     ws[w] = SA;
-    ws[kCtcWarps + w] = SB;
+    ws[NCW + w] = SB;
   }
   float ea = __shfl_up_sync(FULLMASK, SA, 1);
   float eb = __shfl_up_sync(FULLMASK, SB, 1);
@@ -142,12 +144,12 @@ __device__ __noinline__ void group_affine_scan(const float* a, const float* b, f
     ea = 0.f;
     eb = LGASR_NEG;
   }
-  group_bar(bar_id, kCtcThreads);
+  group_bar(bar_id, NCT);
   // summaries of the preceding warps followed by this thread's exclusive prefix inside the warp
   float XA = 0.f, XB = LGASR_NEG;
 #pragma unroll 1
   for (int i = 0; i <= w; ++i) {
-    const float wa = (i < w) ? ws[i] : ea, wb = (i < w) ? ws[kCtcWarps + i] : eb;
+    const float wa = (i < w) ? ws[i] : ea, wb = (i < w) ? ws[NCW + i] : eb;
     XB = lse2(XB + wa, wb);
     XA += wa;
   }
@@ -159,7 +161,7 @@ __device__ __noinline__ void group_affine_scan(const float* a, const float* b, f
     run += a[t];
     y[t] = lse2(yin + run, y[t]);
   }
-  group_bar(bar_id, kCtcThreads);
+  group_bar(bar_id, NCT);
 }
 
 // CTC state of hypothesis (b, h) by the ctc group.
@@ -174,6 +176,7 @@ __device__ __noinline__ void group_affine_scan(const float* a, const float* b, f
 //   bR0[u] = r_sum[u-1]   and   bR1[u] = r^b[u-1]   for pstart <= u < T, LGASR_NEG elsewhere
 // (pstart = max(olen, 1) of THIS hypothesis): the phi arrays of the psi phase, shifted by one frame so that
 // phi[t-1] + x[t] is an aligned element-wise sum.  *psi_eos = r_sum[T-1].
+template <int NCW>
 __device__ __forceinline__ void group_ctc_scans(const float* bR1, const float* bA, float* bB, const float* bC, float* bD,
                                                 int has_parent, int par_initial, int same, int olen_par, int T, int g,
                                                 float* ws, int bar_id, long long* tr) {
@@ -184,17 +187,17 @@ __device__ __forceinline__ void group_ctc_scans(const float* bR1, const float* b
     rn0 = (olen_par == 0) ? bA[0] : LGASR_LOGZERO;               // r[start-1, 0]  (:128-129)
     // r^n: a = x_tok, b[t] = phi_parent[t-1] + x_tok[t]; phi = r_sum, or r^b for a repeated token (:131-140)
 #pragma unroll 1
-    for (int t = start + g; t < T; t += kCtcThreads) {
+    for (int t = start + g; t < T; t += 32 * NCW) {
       const int u = t - 1;
       float phi = bR1[u];
       if (same && !par_initial) phi = (u >= start_par) ? bR1[u - 1] + bC[u] : LGASR_LOGZERO;
       bB[t] = phi + bA[t];
     }
-    group_bar(bar_id, kCtcThreads);
-    group_affine_scan(bA, bB, bB, start, T, rn0, g, ws, bar_id);
+    group_bar(bar_id, 32 * NCW);
+    group_affine_scan<NCW>(bA, bB, bB, start, T, rn0, g, ws, bar_id);
     if (tr && g == 0) tr[8] = clock64();
     // r_sum: a = x_blank, b[t] = r^n[t]   (s_t = lse2(r^b_t, r^n_t), r^b_t = s_{t-1} + x_blank[t])
-    group_affine_scan(bC, bB, bD, start, T, rn0, g, ws, bar_id);
+    group_affine_scan<NCW>(bC, bB, bD, start, T, rn0, g, ws, bar_id);
     if (tr && g == 0) tr[9] = clock64();
   }
 }
@@ -257,14 +260,14 @@ struct __align__(16) StepSmem {
   int n_top, cur_list;
   float w_eos, psi_eos;
   int last_flag, pad0;
-  float ws[2 * kCtcWarps];
-  unsigned wkth[kSelWarps];
+  float ws[2 * kStepWarps];
+  unsigned wkth[kStepWarps];
 };
 
 // debug time line: stamp i of group grp (0 ctc / all, 1 sel) of this CTA
 #define LGASR_TR(grp, i)                                                                       \
   do {                                                                                          \
-    if (TR && tid == ((grp) ? kCtcThreads : 0))                                                 \
+    if (TR && tid == ((grp) ? SEL0 : 0))                                                 \
       d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2 + (grp)) * 16 + (i)] = clock64(); \
   } while (0)
 
@@ -275,7 +278,7 @@ __device__ __forceinline__ long long gtimer() {
 }
 #define LGASR_GT(i)                                                                                     \
   do {                                                                                                  \
-    if (TR && tid == 0) d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 + (i)] = gtimer(); \
+    if (TR && tid == 0) d.trace[((long long)(blockIdx.y * d.W + blockIdx.x) * 2 + (step & 1)) * 16 + (i)] = gtimer(); \
   } while (0)
 
 // ---- thread-block cluster helpers (one cluster = the `beam` CTAs of an utterance) -------------------------
@@ -383,10 +386,18 @@ __device__ __forceinline__ float4 fused4(const Terms& tm, const float* sb, int C
 // CL: launched as clusters of `beam` CTAs (cluster rank == hypothesis slot): the candidate records and the
 // parents' fields travel to the shared memory of the rank-0 CTA (distributed shared memory) and a cluster
 // barrier replaces the fence + atomic ticket and the exchange through L2; rank 0 runs the selection.
-template <bool TR, bool CL>
+// SEQ (launches with programmatic stream serialization, i.e. the positions after the first of a replay): the
+// row stream + top-S selection depends only on inputs of the step, so ALL eight warps run it BEFORE
+// griddepcontrol.wait, overlapped with the previous position's selection tail; after the wait the CTC scans get
+// four warps instead of two.  !SEQ: the two groups run side by side after the wait (2 + 6 warps).
+template <bool TR, bool CL, bool SEQ>
 __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepLaunch sl, int pp, int rp, int step) {
+  constexpr int NCW = SEQ ? 4 : kCtcWarps, NCT = 32 * NCW;      // ctc group: warps [0, NCW)
+  constexpr int NSW = SEQ ? kStepWarps : kSelWarps, NSG = 32 * NSW;  // sel group: threads [SEL0, SEL0 + NSG)
+  constexpr int SEL0 = SEQ ? 0 : kCtcThreads;
   const int b = blockIdx.y, h = blockIdx.x;
   const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
   const int W = d.W, V = d.V, Tp = d.Tp;
   const int row = b * W + h;
   const long long rowoff = (long long)row * tm.ld;
@@ -403,13 +414,16 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   const int nchunks = sl.nchunks;
   const bool tma = sl.tma_rows != 0;
   const int mode = d.mode;
+  const float* xT_b = d.xT + (long long)b * V * Tp;
+  const int n_sel = (mode == kModePreBeam) ? d.S : d.W;
   // ---- programmatic dependent launch: everything up to griddepcontrol.wait touches only kernel parameters,
-  // this CTA's shared memory and the full-scorer matrices (inputs of the step, never written by the previous
-  // k_step), so under PDL it overlaps the previous position's selection tail: the next grid's CTAs take the
-  // slots of CTAs that have left and have their score rows in flight before the previous grid has drained.
+  // this CTA's shared memory and inputs of the step (the full-scorer matrices and the posteriors, never written
+  // by a k_step), so under PDL it overlaps the previous position's selection tail: the next grid's CTAs take the
+  // slots of CTAs that have left.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  LGASR_GT(13);  // kernel entry (before griddepcontrol.wait)
   if (CL) cluster_arrive();  // phase 1: "this CTA runs"; waited for before the first remote store
-  if (tid == kCtcThreads) {
+  if (tid == SEL0) {
 #pragma unroll
     for (int i = 0; i < kMaxStages; ++i) mbar_init(reinterpret_cast<uint64_t*>(&S->bar_full[i]), 1);
 #pragma unroll
@@ -426,79 +440,15 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
       for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
     }
   }
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  // per-hypothesis metadata: one batch of independent loads (rows h >= n_run hold stale but valid memory)
-  const int done = d.done[pp][b], n_run = d.n_run[pp][b];
-  const int T = d.xlen[b];
-  const int cur_len = d.cur_len[pp][b];
-  const int4 rm = d.rmeta[pp][row];  // parent slot, last token, parent's last token
-  const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
-  const float hyp_score = d.score[pp][row];
-  const int maxlen_b = d.maxlen[b], minlen_b = d.minlen[b];  // for the selection (no dependent load there)
-  // cluster variant: this hypothesis' fields the selection needs of its parents, sent to rank 0 later
-  const int my_slot = CL ? d.run_slot[pp][row] : 0;
-  const float my_sc = (CL && tid < d.NS) ? d.scores[pp][(long long)row * d.NS + tid] : 0.f;
-  if (done || h >= n_run) {
-    if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
-    // the row copies already in flight target this CTA's shared memory: let them land before leaving
-    if (tid == kCtcThreads && sl.pdl && tma && mode != kModeFullCtc) {
-      const int pre = nchunks < NST ? nchunks : NST;
-      for (int c = 0; c < pre; ++c) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[c]), 0);
-    }
-    if (CL) {  // an idle CTA still takes part in both phases of the cluster barrier
-      __syncwarp();
-      cluster_wait();
-      cluster_arrive();
-    }
-    return;
-  }
 
-  const int lane = tid & 31, warp = tid >> 5;
-  const int olen = cur_len - 1;
-  const int last = rm.y;
-  const float* xT_b = d.xT + (long long)b * V * Tp;
-  const int n_sel = (mode == kModePreBeam) ? d.S : d.W;
-  const int has_parent = rm.x >= 0;
-
-  // the two issuing threads initialise their own mbarriers and start their TMA copies before the CTA barrier
-  if (tid == 0) {
-    mbar_init(reinterpret_cast<uint64_t*>(&S->bar_ctc), 1);
-    mbar_fence_init();
-    if (d.use_ctc) {
-      const float* r_par = d.r[rp] + ((long long)(b * W + (has_parent ? rm.x : h)) * 2) * Tp;
-      const uint32_t rb = (uint32_t)Tp * 4u;
-      mbar_expect_tx(reinterpret_cast<uint64_t*>(&S->bar_ctc), has_parent ? 4u * rb : 2u * rb);
-      bulk_g2s(bR0, r_par, 2u * rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
-      if (has_parent) {
-        bulk_g2s(bA, xT_b + (long long)last * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
-        bulk_g2s(bC, xT_b + (long long)d.blank * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
-      }
-    }
-  } else if (tid == kCtcThreads && !sl.pdl && tma && mode != kModeFullCtc) {
-    const int pre = nchunks < NST ? nchunks : NST;
-    for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
-  }
-  __syncthreads();
-  LGASR_TR(0, 0);
-  LGASR_TR(1, 0);
-  LGASR_GT(14);
-
-  if (tid < kCtcThreads) {
-    // ======================= ctc group: CTC state of this hypothesis ==================================
-    if (d.use_ctc) {
-      mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
-      LGASR_TR(0, 1);
-      group_ctc_scans(bR1, bA, bB, bC, bD, has_parent, step == 1, last == rm.z, olen - 1, T, tid, S->ws, kBarCtc,
-                      TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
-      LGASR_TR(0, 2);
-    }
-  } else if (mode != kModeFullCtc) {
+  // ======================= sel group: fused row stream + exact top-n_sel ================================
+  auto sel_phase = [&]() {
     // ======================= sel group: fused row stream + exact top-n_sel ============================
     // Two sweeps over each staged chunk: lane maxima -> threshold (only while the list is not full), then
     // push everything above the threshold into a pending list (warp-aggregated shared atomics) and merge
     // by rank counting on packed (value, ~index) keys.  A pending-list overflow (degenerate rows, e.g. all
     // scores equal) is handled by extra rounds over the same chunk with the tightened threshold.
-    const int j = tid - kCtcThreads;
+    const int j = tid - SEL0;
     const int wj = j >> 5;
     const int key = d.key;
     const int srows = tm.nptr > 0 ? tm.nptr : 1;
@@ -520,9 +470,9 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           if (!src) continue;
           src += rowoff + e0;
           float* dst = sb + tm.slot[k] * CH;
-          for (int i = j; i < n_ch; i += kSelGroup) dst[i] = __ldg(src + i);
+          for (int i = j; i < n_ch; i += NSG) dst[i] = __ldg(src + i);
         }
-        group_bar(kBarSel, kSelGroup);
+        group_bar(kBarSel, NSG);
       }
       if (c == 0) LGASR_TR(1, 1);
       // ---- sweep 1: fuse the K terms in place (term-major, so the fp32 order is the reference's
@@ -534,7 +484,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
       if (one_term) {  // the common shape (decoder only): w0 * s0, no tail
         const float w0 = tm.w[0];
 #pragma unroll 2
-        for (int q = j; q < nq; q += kSelGroup) {
+        for (int q = j; q < nq; q += NSG) {
           float4 v = fz[q];
           v.x = __fmul_rn(w0, v.x);  // 0 + w0*s0 == w0*s0 (up to the sign of zero)
           v.y = __fmul_rn(w0, v.y);  // 0 + w0*s0 == w0*s0 (up to the sign of zero)
@@ -545,7 +495,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         }
       } else
 #pragma unroll 1
-      for (int q = j; q < nq; q += kSelGroup) {
+      for (int q = j; q < nq; q += NSG) {
         float4 acc;
         if (key >= 0) {
           acc = fz[q];
@@ -578,14 +528,14 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         mx = fmaxf(fmaxf(mx, fmaxf(acc.x, acc.y)), fmaxf(acc.z, acc.w));
       }
       // the fused score of eos is needed even when eos is not a pre-beam candidate (:180-181)
-      if (key < 0 && d.eos >= e0 && d.eos < e0 + n_ch && (((d.eos - e0) >> 2) % kSelGroup) == j)
+      if (key < 0 && d.eos >= e0 && d.eos < e0 + n_ch && (((d.eos - e0) >> 2) % NSG) == j)
         S->w_eos = reinterpret_cast<const float*>(fz)[d.eos - e0];
       unsigned long long thr = tau;
       if (n_top < n_sel) {
         // ---- threshold of a chunk met with a non-full list: at least n_sel elements of the chunk are >=
         //      the kk-th largest lane maximum of every active warp (kk = ceil(n_sel / active warps)) ------
-        const int nw_act = min(kSelWarps, (nq + 31) >> 5);
-        const int kk = (nw_act == kSelWarps) ? sl.kk_full : (n_sel + nw_act - 1) / nw_act;
+        const int nw_act = min(NSW, (nq + 31) >> 5);
+        const int kk = (!SEQ && nw_act == NSW) ? sl.kk_full : (n_sel + nw_act - 1) / nw_act;
         unsigned co = (mx > -INFINITY) ? f2ord(mx + 0.0f) : 0u;
         unsigned kth = 0u;
         for (int r = 0; r < kk; ++r) {
@@ -594,10 +544,10 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           if (lane == __ffs(holders) - 1) co = 0u;
         }
         if (lane == 0) S->wkth[wj] = (wj < nw_act) ? kth : 0xffffffffu;  // idle warps do not vote
-        group_bar(kBarSel, kSelGroup);
+        group_bar(kBarSel, NSG);
         unsigned mn = S->wkth[0];
 #pragma unroll
-        for (int w2 = 1; w2 < kSelWarps; ++w2) mn = min(mn, S->wkth[w2]);
+        for (int w2 = 1; w2 < NSW; ++w2) mn = min(mn, S->wkth[w2]);
         const unsigned long long thr_c = (mn == 0u) ? 0ull : (((unsigned long long)mn << 32) | 0x80000000ull);
         thr = thr_c > thr ? thr_c : thr;
         if (c == 0) LGASR_TR(1, 3);
@@ -626,7 +576,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           }
         };
 #pragma unroll 1
-        for (int q = j; q < nq; q += kSelGroup) {
+        for (int q = j; q < nq; q += NSG) {
           const float4 v = fz[q];
           if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) >= thr_v) {
             push(v.x, 4 * q);
@@ -635,7 +585,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
             push(v.w, 4 * q + 3);
           }
         }
-        group_bar(kBarSel, kSelGroup);  // A: pushes done, every thread has read its stage values
+        group_bar(kBarSel, NSG);  // A: pushes done, every thread has read its stage values
         const int cnt = S->pend_cnt[p];
         const int ovf = S->overflow[p];
         if (!ovf && tma && j == 0 && c + NST < nchunks) {
@@ -648,7 +598,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           unsigned long long* kn = S->keys[cur ^ 1];
           const ulonglong2* ks2 = reinterpret_cast<const ulonglong2*>(ks);
           const int n2 = n >> 1;
-          for (int e = j; e < n; e += kSelGroup) {
+          for (int e = j; e < n; e += NSG) {
             const unsigned long long ke = ks[e];
             int rank = 0;
 #pragma unroll 4
@@ -660,7 +610,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
             if (n & 1) rank += (ks[n - 1] > ke) ? 1 : 0;
             if (rank < n_sel) kn[rank] = ke;
           }
-          group_bar(kBarSel, kSelGroup);  // B: the merged list is complete
+          group_bar(kBarSel, NSG);  // B: the merged list is complete
           if (j == 0) {
             S->pend_cnt[p] = 0;
             S->overflow[p] = 0;
@@ -685,6 +635,79 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     // ---- gather the candidates' posterior rows (first group) by TMA ------------------------------------
     if (mode == kModePreBeam && wj == 0)
       issue_cand_rows(d, S->keys[cur], 0, n_top < sl.rows_per_group ? n_top : sl.rows_per_group, xT_b, arena, S, lane);
+  };
+  if (SEQ) {
+    __syncthreads();  // the header and the mbarriers are initialised
+    LGASR_TR(1, 0);
+    if (mode != kModeFullCtc) sel_phase();
+  }
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // per-hypothesis metadata: one batch of independent loads (rows h >= n_run hold stale but valid memory)
+  const int done = d.done[pp][b], n_run = d.n_run[pp][b];
+  const int T = d.xlen[b];
+  const int cur_len = d.cur_len[pp][b];
+  const int4 rm = d.rmeta[pp][row];  // parent slot, last token, parent's last token
+  const float s_prev = d.use_ctc ? d.s_prev[pp][row] : 0.f;
+  const float hyp_score = d.score[pp][row];
+  const int maxlen_b = d.maxlen[b], minlen_b = d.minlen[b];  // for the selection (no dependent load there)
+  // cluster variant: this hypothesis' fields the selection needs of its parents, sent to rank 0 later
+  const int my_slot = CL ? d.run_slot[pp][row] : 0;
+  const float my_sc = (CL && tid < d.NS) ? d.scores[pp][(long long)row * d.NS + tid] : 0.f;
+  if (done || h >= n_run) {
+    if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
+    // copies already in flight target this CTA's shared memory: let them land before leaving
+    if (SEQ) {
+      if (mode == kModePreBeam) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand[warp]), 0);
+    } else if (tid == SEL0 && sl.pdl && tma && mode != kModeFullCtc) {
+      const int pre = nchunks < NST ? nchunks : NST;
+      for (int c = 0; c < pre; ++c) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_full[c]), 0);
+    }
+    if (CL) {  // an idle CTA still takes part in both phases of the cluster barrier
+      __syncwarp();
+      cluster_wait();
+      cluster_arrive();
+    }
+    return;
+  }
+
+  const int olen = cur_len - 1;
+  const int last = rm.y;
+  const int has_parent = rm.x >= 0;
+
+  // the two issuing threads initialise their own mbarriers and start their TMA copies before the CTA barrier
+  if (tid == 0) {
+    mbar_init(reinterpret_cast<uint64_t*>(&S->bar_ctc), 1);
+    mbar_fence_init();
+    if (d.use_ctc) {
+      const float* r_par = d.r[rp] + ((long long)(b * W + (has_parent ? rm.x : h)) * 2) * Tp;
+      const uint32_t rb = (uint32_t)Tp * 4u;
+      mbar_expect_tx(reinterpret_cast<uint64_t*>(&S->bar_ctc), has_parent ? 4u * rb : 2u * rb);
+      bulk_g2s(bR0, r_par, 2u * rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
+      if (has_parent) {
+        bulk_g2s(bA, xT_b + (long long)last * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
+        bulk_g2s(bC, xT_b + (long long)d.blank * Tp, rb, reinterpret_cast<uint64_t*>(&S->bar_ctc));
+      }
+    }
+  } else if (!SEQ && tid == SEL0 && !sl.pdl && tma && mode != kModeFullCtc) {
+    const int pre = nchunks < NST ? nchunks : NST;
+    for (int c = 0; c < pre; ++c) issue_row_chunk(tm, rowoff, c, CH, NST, V, arena, S);
+  }
+  __syncthreads();
+  LGASR_TR(0, 0);
+  if (!SEQ) LGASR_TR(1, 0);
+  LGASR_GT(14);
+
+  if (tid < NCT) {
+    // ======================= ctc group: CTC state of this hypothesis ==================================
+    if (d.use_ctc) {
+      mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
+      LGASR_TR(0, 1);
+      group_ctc_scans<NCW>(bR1, bA, bB, bC, bD, has_parent, step == 1, last == rm.z, olen - 1, T, tid, S->ws, kBarCtc,
+                           TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
+      LGASR_TR(0, 2);
+    }
+  } else if (!SEQ && mode != kModeFullCtc) {
+    sel_phase();
   }
   __syncthreads();
   if (d.use_ctc)

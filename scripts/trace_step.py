@@ -46,7 +46,19 @@ last = tr[:, 0, 7] > tr[:, 0, 6]
 d = lambda a, b_: np.median((tr[last, 0, a] - tr[last, 0, b_]).astype(np.float64))
 print(f"select CTAs: n={last.sum()} ticket->loaded {d(12, 6):.0f}  loaded->ranked {d(10, 12):.0f}  ranked->booked {d(11, 10):.0f}  booked->done {d(7, 11):.0f}  total {d(7, 6):.0f}")
 
-g0, g1 = tr[:, 0, 14], tr[:, 0, 15]
+# globaltimer stamps (CTA start / end) alternate between the two rows by step parity: the last two launches
+cur, prv = (L - 1) & 1, L & 1
+g0, g1 = tr[:, cur, 14], tr[:, cur, 15]
+p0, p1 = tr[:, prv, 14], tr[:, prv, 15]
+early = np.sort(g0 - p1.max())
+print(f"consecutive launches: previous grid first start -> last end {(p1.max() - p0.min()) / 1e3:.2f} us; this grid's first CTA starts "
+      f"{(g0.min() - p1.max()) / 1e3:+.2f} us after the previous grid's last CTA ended (median CTA {np.median(early) / 1e3:+.2f} us, last {early[-1] / 1e3:+.2f} us); "
+      f"period (last end -> last end) {(g1.max() - p1.max()) / 1e3:.2f} us; previous grid's non-select CTAs all ended {(p1.max() - np.sort(p1)[int(0.9 * len(p1)) - 1]) / 1e3:.2f} us before its last end")
+en, pen = tr[:, cur, 13], tr[:, prv, 13]
+q = lambda a: " ".join(f"{v / 1e3:+.2f}" for v in np.percentile(a, [0, 10, 50, 90, 100]))
+print(f"kernel entry (before griddepcontrol.wait), us relative to the previous grid's last CTA end, min/p10/p50/p90/max: this grid {q(en - p1.max())}; "
+      f"previous grid's entries {q(pen - p1.max())}, its post-wait starts {q(p0 - p1.max())}, its ends {q(p1 - p1.max())}")
+print(f"this grid: post-wait start {q(g0 - p1.max())}; end {q(g1 - p1.max())}")
 print(f"globaltimer: CTA starts spread {(g0.max() - g0.min()) / 1e3:.2f} us; first start -> last end {(g1.max() - g0.min()) / 1e3:.2f} us; "
       f"median CTA life {np.median(g1 - g0) / 1e3:.2f} us; last ticket-CTA end - first start: {(g1[~last].max() - g0.min()) / 1e3:.2f} us")
 
