@@ -40,7 +40,7 @@ sys.path.insert(0, ROOT)
 
 CFG = dict(B=64, T=374, V=5000, beam=10, S=15, ctc_weight=0.3, L=64, K=1)
 # dram__bytes_read.sum + dram__bytes_write.sum of one steady-state k_step launch (ncu --set full, profiles/)
-TRAFFIC_BYTES_PER_LAUNCH = 33177088  # profiles/r01f: 30.36 MB read + 2.82 MB written
+TRAFFIC_BYTES_PER_LAUNCH = 34591744  # profiles/r01h: 30.24 MB read + 4.35 MB written (k_step<0,0,1>)
 AUDIO_SEC = 15.0
 
 

@@ -234,6 +234,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     rc |= dalloc(h, &d.rmeta[p], BW);
   }
   rc |= dalloc(h, &d.arrive, d.B);
+  rc |= dalloc(h, &d.step_flag, d.B);
   if (getenv("LGASR_TRACE")) {
     rc |= dalloc(h, &d.trace, BW * 32);
     if (!rc) cudaMemset(d.trace, 0, BW * 32 * sizeof(long long));
@@ -470,7 +471,7 @@ static int fill_terms(lgasr_handle* h, Terms& tm, const float* const* ptr, const
   return LGASR_OK;
 }
 
-static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl = false) {
+static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl = false, bool flags = false) {
   Dev& d = h->d;
   if (h->step >= d.maxlen_cap) return fail(LGASR_ESTATE, "step %d beyond max_len_cap %d", h->step, d.maxlen_cap);
   dim3 grid(d.W, d.B);
@@ -520,6 +521,7 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     cfg.attrs = at;
     cfg.numAttrs = na;
     sl.pdl = pdl ? 1 : 0;
+    sl.flags = flags ? 1 : 0;
     auto kern = k_step<false, false, false>;
     if (use_cluster) {
       if (d.trace) kern = seq ? k_step<true, true, true> : k_step<true, true, false>;
@@ -776,11 +778,15 @@ extern "C" int lgasr_decode_replay(lgasr_handle* h, int n_steps, const float* co
   cudaStream_t st = user_st;
   const char* npdl = getenv("LGASR_NO_PDL");
   const bool pdl = !h->profiling && !(npdl && npdl[0] == '1');
+  // experimental (off by default, +1 % at configs[1]): per-utterance release/acquire flags instead of the grid-wide
+  // griddepcontrol.wait between the positions of a replay
+  const char* fl = getenv("LGASR_FLAGS");
+  const bool flags = pdl && fl && fl[0] == '1';
   auto run_steps = [&]() -> int {
     for (int i = 0; i < n_steps; ++i) {
       Terms tm;
       TRY(fill_terms(h, tm, h_term_ptr ? h_term_ptr + (size_t)i * K : nullptr, h_term_const, h_term_weight, ld));
-      TRY(step_impl(h, tm, st, pdl && i > 0));
+      TRY(step_impl(h, tm, st, pdl && i > 0, flags));
     }
     return LGASR_OK;
   };

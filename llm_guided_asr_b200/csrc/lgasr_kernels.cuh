@@ -46,6 +46,7 @@ struct Dev {
   int* done[2];          // [B]
   int4* rmeta[2];        // [B][W] (parent slot or -1, last token, parent's last token or -1, 0)
   int* arrive;           // [B] CTAs of the utterance that finished scoring in the current launch
+  int* step_flag;        // [B] decode positions of the utterance whose selection is complete (release / acquire)
   int* step_parent;      // [B][W]
   int* step_tok;         // [B][W]
   const int* maxlen;     // [B]
@@ -791,6 +792,7 @@ __global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_
       d.done[p][b] = (d.maxlen[b] <= 0) ? 1 : 0;
     }
     d.arrive[b] = 0;
+    d.step_flag[b] = 0;
     d.n_ended[b] = 0;
     d.best_all[b] = -INFINITY;
   }

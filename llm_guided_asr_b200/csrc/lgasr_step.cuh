@@ -35,6 +35,8 @@ struct StepLaunch {
   int NST;             // stages in flight (1 or 2)
   int nchunks;         // ceil(V / CH)
   int kk_full;         // ceil(n_sel / kSelWarps): lane-maximum rounds of the chunk threshold
+  int flags;           // replay with LGASR_FLAGS=1: publish step_flag[b] after the selection; SEQ launches acquire it
+                       // instead of griddepcontrol.wait (utterances advance at their own pace)
   int pdl;             // launched with programmatic stream serialization: rows are requested before griddepcontrol.wait
   int tma_rows;        // 1: full-scorer rows are 16-byte aligned -> bulk copies; 0: plain loads
   int arena_floats;    // union buffer: row stages | candidate rows | selection scratch
@@ -295,6 +297,18 @@ __device__ __forceinline__ void st_cluster(uint32_t addr, unsigned long long v) 
 }
 __device__ __forceinline__ void st_cluster(uint32_t addr, unsigned v) {
   asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// per-utterance hand-off between consecutive positions (SEQ launches): the selection of position s publishes
+// step_flag[b] = s + 1 after its last write; the CTAs of position s + 1 acquire it instead of waiting for the
+// whole previous grid (griddepcontrol.wait), so utterances advance at their own pace
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 constexpr int kBarCtc = 1, kBarSel = 2;  // named barriers of the two groups (0 = __syncthreads)
@@ -641,7 +655,18 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     LGASR_TR(1, 0);
     if (mode != kModeFullCtc) sel_phase();
   }
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (SEQ && sl.flags) {
+    // every producer of this utterance's state is a CTA of an earlier grid, resident or gone: no deadlock
+    if (tid == 0) {
+      int spins = 0;
+      while (ld_acquire_gpu(d.step_flag + b) < step)
+        if (++spins > (1 << 22)) __trap();  // a broken chain must fail, not hang the device
+      asm volatile("fence.proxy.async.global;" ::: "memory");  // the parent state is fetched by TMA
+    }
+    __syncthreads();
+  } else {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+  }
   // per-hypothesis metadata: one batch of independent loads (rows h >= n_run hold stale but valid memory)
   const int done = d.done[pp][b], n_run = d.n_run[pp][b];
   const int T = d.xlen[b];
@@ -654,7 +679,10 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   const int my_slot = CL ? d.run_slot[pp][row] : 0;
   const float my_sc = (CL && tid < d.NS) ? d.scores[pp][(long long)row * d.NS + tid] : 0.f;
   if (done || h >= n_run) {
-    if (h == 0 && tid == 0 && (done || n_run <= 0)) utt_carry_done(d, b, pp);
+    if (h == 0 && tid == 0 && (done || n_run <= 0)) {
+      utt_carry_done(d, b, pp);
+      if (sl.flags) st_release_gpu(d.step_flag + b, step + 1);
+    }
     // copies already in flight target this CTA's shared memory: let them land before leaving
     if (SEQ) {
       if (mode == kModePreBeam) mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_cand[warp]), 0);
@@ -880,6 +908,10 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   }
   LGASR_TR(0, 7);
   LGASR_GT(15);
+  if (sl.flags) {
+    __syncthreads();  // every thread's writes of the selection, then one (cumulative) release by thread 0
+    if (tid == 0) st_release_gpu(d.step_flag + b, step + 1);
+  }
 }
 
 }  // namespace lgasr

@@ -59,6 +59,14 @@ q = lambda a: " ".join(f"{v / 1e3:+.2f}" for v in np.percentile(a, [0, 10, 50, 9
 print(f"kernel entry (before griddepcontrol.wait), us relative to the previous grid's last CTA end, min/p10/p50/p90/max: this grid {q(en - p1.max())}; "
       f"previous grid's entries {q(pen - p1.max())}, its post-wait starts {q(p0 - p1.max())}, its ends {q(p1 - p1.max())}")
 print(f"this grid: post-wait start {q(g0 - p1.max())}; end {q(g1 - p1.max())}")
+# per utterance: the chain from one position's selection to the next one's
+G0, G1, EN, P1 = g0.reshape(B, W), g1.reshape(B, W), en.reshape(B, W), p1.reshape(B, W)
+u_prev_end, u_end = P1.max(axis=1), G1.max(axis=1)
+u_start = G0.max(axis=1)
+print(f"per utterance (us, medians): previous selection end -> all CTAs past the hand-off {np.median(u_start - u_prev_end) / 1e3:.2f}; "
+      f"hand-off -> selection end {np.median(u_end - u_start) / 1e3:.2f}; period (selection end -> selection end) {np.median(u_end - u_prev_end) / 1e3:.2f} "
+      f"(p10 {np.percentile(u_end - u_prev_end, 10) / 1e3:.2f}, p90 {np.percentile(u_end - u_prev_end, 90) / 1e3:.2f}); "
+      f"entry -> past the hand-off (selection phase + waiting) {np.median(G0 - EN) / 1e3:.2f}; entry - previous selection end {np.median(EN - u_prev_end[:, None]) / 1e3:+.2f}")
 print(f"globaltimer: CTA starts spread {(g0.max() - g0.min()) / 1e3:.2f} us; first start -> last end {(g1.max() - g0.min()) / 1e3:.2f} us; "
       f"median CTA life {np.median(g1 - g0) / 1e3:.2f} us; last ticket-CTA end - first start: {(g1[~last].max() - g0.min()) / 1e3:.2f} us")
 
