@@ -179,3 +179,66 @@ def _replay_host_equals_stepping():
             assert t[0] == eos and t[-1] == eos and len(t) == L + 2
         assert all(np.isfinite(score))
     eng.close()
+
+
+@pytest.mark.parametrize(
+    "V,names,key,use_ctc,consts,flags",
+    [
+        (20000, ["decoder", "lm"], "full", True, None, "0"),  # two matrices, 2-stage ring, many chunks
+        (20000, ["decoder", "lm"], "full", True, None, "1"),  # ... with the per-utterance flag hand-off
+        (1001, ["decoder", "lm"], "full", True, None, "0"),  # vocabulary not a multiple of 4: plain-load staging
+        (3000, ["decoder", "lm"], "decoder", True, None, "0"),  # pre-beam on one scorer
+        (3000, ["decoder", "length_bonus"], "full", True, 1.0, "0"),  # a constant term
+        (2000, ["decoder"], None, False, None, "0"),  # no CTC scorer: top-beam per hypothesis
+    ],
+)
+def test_replay_instances_equal_stepping_on_every_staging_path(monkeypatch, V, names, key, use_ctc, consts, flags):
+    """The replay (CUDA graph + programmatic dependent launch: the SEQ instance of k_step, selection before
+    griddepcontrol.wait, four CTC warps) must reproduce position-by-position stepping (the side-by-side
+    instance) bit for bit on every staging path; ragged lengths, an utterance that finishes early."""
+    from llm_guided_asr_b200.engine import FusedStepEngine
+    from llm_guided_asr_b200 import synthetic as syn
+
+    monkeypatch.setenv("LGASR_FLAGS", flags)
+    dev = torch.device("cuda:0")
+    B, T, W, L = 5, 70, 6, 10
+    eos = V - 1
+    lens = [70, 41, 70, 9, 55]
+    logp = torch.stack([syn.random_logp(60 + b, T, V) for b in range(B)]).to(dev)
+    g = torch.Generator().manual_seed(V)
+    nmat = sum(1 for n in names if n != "length_bonus")
+    tabs = torch.log_softmax(2.0 * torch.randn(L, nmat, B * W, V, generator=g), dim=-1).to(dev)
+    wts = [0.7, 0.4][: len(names)]
+    cst = [0.0] * len(names)
+    if consts is not None:
+        cst[names.index("length_bonus")] = consts
+    eng = FusedStepEngine(B, T, V, W, int(1.5 * W), names, key, use_ctc, 0.3, eos, eos, L, 1, True, device=dev)
+    mx, mn = [L, L, L, 3, L], [0] * B  # utterance 3 stops after 3 positions
+
+    def mats(i):
+        out, m = [], 0
+        for n in names:
+            if n == "length_bonus":
+                out.append(None)
+            else:
+                out.append(tabs[i, m])
+                m += 1
+        return out
+
+    def collect():
+        return [tuple(np.asarray(a).tolist() for a in eng.gather_ended(b)[:2]) for b in range(B)]
+
+    eng.set_posteriors(logp if use_ctc else None, lens)
+    eng.begin(mx, mn, [eos])
+    for i in range(L):
+        eng.step(mats(i), cst, wts)
+        if eng.poll(with_parents=False)[4] == 0:
+            break
+    stepped = collect()
+    assert any(len(t) for t, _ in stepped)
+    for _ in range(2):
+        eng.set_posteriors(logp if use_ctc else None, lens)
+        eng.begin(mx, mn, [eos])
+        eng.replay([mats(i) for i in range(L)], cst, wts, ld=V)
+        assert collect() == stepped
+    eng.close()
