@@ -31,6 +31,11 @@ tr = out.reshape(B * W, 2, 16)
 t0 = tr[:, 0, 0:1]
 names0 = ["start", "ctc_in", "ctc_done", "joined", "cand_in", "records", "ticket", "select_done", "scan1_done", "scan2_done", "sel_ranked", "sel_booked", "sel_loaded"]
 names1 = ["start", "row0_in", "sel_done", "thr_done", "chunk0_done"]
+rel0 = None  # filled after the selection stamps have been masked
+# CTAs that ran the selection in THIS launch (slots 7, 10-12 of the others hold stamps of earlier launches)
+last = (tr[:, 0, 7] > tr[:, 0, 6]) & (tr[:, 0, 7] - tr[:, 0, 6] < 1_000_000) & (tr[:, 0, 12] > tr[:, 0, 6])
+for i in (7, 10, 11, 12):
+    tr[~last, 0, i] = 0
 rel0 = (tr[:, 0, :13] - t0).astype(np.float64)
 rel1 = (tr[:, 1, :5] - t0).astype(np.float64)
 for i, n in enumerate(names0):
@@ -42,7 +47,7 @@ for i, n in enumerate(names1):
     if len(v):
         print(f"sel     {n:12s} n={len(v):4d} median={np.median(v):9.0f} p90={np.percentile(v, 90):9.0f} max={v.max():9.0f} cycles")
 
-last = tr[:, 0, 7] > tr[:, 0, 6]
+
 d = lambda a, b_: np.median((tr[last, 0, a] - tr[last, 0, b_]).astype(np.float64))
 print(f"select CTAs: n={last.sum()} ticket->loaded {d(12, 6):.0f}  loaded->ranked {d(10, 12):.0f}  ranked->booked {d(11, 10):.0f}  booked->done {d(7, 11):.0f}  total {d(7, 6):.0f}")
 
