@@ -62,14 +62,21 @@ class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
     protocol (e.g. under the reference's own search) it simply delegates to the wrapped decoder.
     """
 
-    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True):
+    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
         torch.nn.Module.__init__(self)
         for name in ("embed", "decoders", "output_layer"):
             if not hasattr(decoder, name):
                 raise TypeError(f"decoder has no attribute {name!r}: not a BaseTransformerDecoder-like module")
         self.decoder = decoder
         self.fused_log_softmax = fused_log_softmax
+        # cuda_graphs: the decoder call of a position (embed -> layers -> output layer -> log-softmax) is captured
+        # once per prefix length into a CUDA graph over static buffers and replayed for every later batch of the
+        # same shape: an eager decoder step is ~25 launches per layer, i.e. launch-bound at beam-search sizes
+        self.cuda_graphs = cuda_graphs
         self._eng = None
+        self._shape = None
+        self._graphs = {}
+        self._pool = None
 
     # ---- plain scorer protocol: delegate ------------------------------------------------------------------
     def batch_init_state(self, x):
@@ -90,30 +97,38 @@ class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
         B, W = engine.cfg.n_utts, engine.cfg.beam
         dev = xs[0].device
         T = max(int(t) for t in lens)
-        mem = xs[0].new_zeros(B, T, xs[0].shape[-1])
+        shape = (B, W, T, int(xs[0].shape[-1]), int(max_positions), engine.cfg.vocab, xs[0].dtype, dev)
+        if shape != self._shape:  # static buffers (and the graphs captured over them) live as long as the shape
+            self._shape = shape
+            self._graphs, self._pool = {}, None
+            self._memory = xs[0].new_zeros(B * W, T, xs[0].shape[-1])
+            self._memory_mask = torch.zeros(B * W, 1, T, dtype=torch.bool, device=dev)
+            self._tgt = torch.zeros(B * W, int(max_positions), dtype=torch.int64, device=dev)
+            self._out = torch.empty(B * W, engine.cfg.vocab, dtype=torch.float32, device=dev)
+            self._buf = None  # [2] x (n_layers, B*W, cap, Dm), allocated on the first call (Dm known then)
+        mem = self._memory.view(B, W, T, -1)
+        mem.zero_()
         for b, x in enumerate(xs):
-            mem[b, : lens[b]] = x
-        self._memory = mem.repeat_interleave(W, dim=0)  # (B*W, T, D)
+            mem[b, :, : lens[b]] = x
         ar = torch.arange(T, device=dev)
         mask = ar[None, :] < torch.as_tensor(list(lens), device=dev)[:, None]  # (B, T)
-        self._memory_mask = mask.repeat_interleave(W, dim=0).unsqueeze(1)  # (B*W, 1, T)
+        self._memory_mask.view(B, W, T).copy_(mask[:, None, :].expand(B, W, T))
         self._eng = engine
         self._cap = int(max_positions)
-        self._buf = None  # [2] x (n_layers, B*W, cap, Dm), allocated on the first call (Dm known then)
         self._pp = 0
         self._new = None
-        self._out = torch.empty(B * W, engine.cfg.vocab, dtype=torch.float32, device=dev)
+        self._fresh = True  # no cache yet in this batch (the persistent buffers may hold the previous batch)
         self._V = engine.cfg.vocab
 
-    def batch_score_padded(self, yseq: torch.Tensor, n_run, done) -> torch.Tensor:
-        """``yseq (B, W, L)`` int64 running prefixes (all row slots) -> ``(B*W, V)`` fp32 log-probabilities;
-        rows of slots that are not running hold values nobody reads."""
+    def _forward(self, L: int):
+        """Decoder call for prefix length ``L`` over the static buffers; writes ``self._out``, returns the new
+        per-layer caches ``(B*W, L, Dm)`` (the body of ``forward_one_step``, transformer_decoder.py:195-212,
+        without its log_softmax)."""
         dec = self.decoder
-        B, W, L = yseq.shape
-        tgt = yseq.reshape(B * W, L).clamp(0, self._V - 1)  # idle slots may hold stale ids
+        tgt = self._tgt[:, :L]
         tgt_mask = torch.ones(L, L, dtype=torch.bool, device=tgt.device).tril().unsqueeze(0)
         nl = len(dec.decoders)
-        if self._buf is None or L == 1:
+        if self._fresh or self._buf is None or L == 1:
             cache = [None] * nl
         else:
             cache = [self._buf[self._pp][i, :, : L - 1] for i in range(nl)]
@@ -127,10 +142,37 @@ class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
         if getattr(dec, "normalize_before", False) and getattr(dec, "after_norm", None) is not None:
             y = dec.after_norm(y)
         logits = dec.output_layer(y)
-        self._new = new
         if self.fused_log_softmax:
-            return log_softmax_rows(logits if logits.dtype in (torch.float32, torch.bfloat16) else logits.float(), self._out)
-        self._out.copy_(torch.log_softmax(logits.float(), dim=-1))
+            log_softmax_rows(logits if logits.dtype in (torch.float32, torch.bfloat16) else logits.float(), self._out)
+        else:
+            self._out.copy_(torch.log_softmax(logits.float(), dim=-1))
+        return new
+
+    def batch_score_padded(self, yseq: torch.Tensor, n_run, done) -> torch.Tensor:
+        """``yseq (B, W, L)`` int64 running prefixes (all row slots) -> ``(B*W, V)`` fp32 log-probabilities;
+        rows of slots that are not running hold values nobody reads."""
+        B, W, L = yseq.shape
+        self._tgt[:, :L].copy_(yseq.reshape(B * W, L).clamp(0, self._V - 1))  # idle slots may hold stale ids
+        if not self.cuda_graphs or self._fresh or self._buf is None:
+            self._new = self._forward(L)
+            return self._out
+        key = (L, self._pp)
+        ent = self._graphs.get(key)
+        if ent is None:
+            cur = torch.cuda.current_stream()
+            side = torch.cuda.Stream()
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):  # warm-up outside the capture (library workspaces, lazy kernels)
+                self._forward(L)
+            cur.wait_stream(side)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, pool=self._pool):
+                new = self._forward(L)
+            if self._pool is None:
+                self._pool = g.pool()
+            ent = self._graphs[key] = (g, new)
+        ent[0].replay()
+        self._new = ent[1]
         return self._out
 
     def device_reorder(self) -> None:
@@ -148,3 +190,4 @@ class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
             self._eng.reorder_rows(dst[i], src.contiguous(), row_elems=L * Dm)
         self._pp ^= 1
         self._new = None
+        self._fresh = False

@@ -41,7 +41,8 @@ def main(B=8, T=374, V=5000, D=256, layers=6, beam=10, L=32):
                                weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
 
     out = {}
-    for name, sc in (("host-state protocol", dec), ("device caches", DeviceCachedDecoderScorer(dec))):
+    for name, sc in (("host-state protocol", dec), ("device caches", DeviceCachedDecoderScorer(dec)),
+                     ("device caches + graphs", DeviceCachedDecoderScorer(dec, cuda_graphs=True))):
         bs = search(sc)
         best = 1e9
         for it in range(4):
@@ -52,12 +53,14 @@ def main(B=8, T=374, V=5000, D=256, layers=6, beam=10, L=32):
             if it:
                 best = min(best, time.perf_counter() - t0)
         out[name] = res
-        print(f"{name:22s}: {best * 1e3:8.1f} ms per batch of {B} utterances x {bs.last_steps} positions "
+        print(f"{name:24s}: {best * 1e3:8.1f} ms per batch of {B} utterances x {bs.last_steps} positions "
               f"({best / bs.last_steps * 1e6:7.0f} us per position, {B / best:7.1f} utts/s)")
-    a, b = out["host-state protocol"], out["device caches"]
-    same = all(x.yseq.tolist() == y.yseq.tolist() for u, v in zip(a, b) for x, y in zip(u, v))
-    dmax = max(abs(float(x.score) - float(y.score)) for u, v in zip(a, b) for x, y in zip(u, v))
-    print(f"n-best lists equal: {same}; max |score difference| {dmax:.2e}")
+    a = out["host-state protocol"]
+    for nm in ("device caches", "device caches + graphs"):
+        b = out[nm]
+        same = all(x.yseq.tolist() == y.yseq.tolist() for u, v in zip(a, b) for x, y in zip(u, v))
+        dmax = max(abs(float(x.score) - float(y.score)) for u, v in zip(a, b) for x, y in zip(u, v))
+        print(f"{nm}: n-best lists equal to the host-state protocol: {same}; max |score difference| {dmax:.2e}")
 
 
 if __name__ == "__main__":

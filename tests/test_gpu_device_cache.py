@@ -160,6 +160,41 @@ def test_device_cached_decoder_decode(fused_lsm):
             assert abs(float(h.score) - float(r.score)) <= SCORE_ATOL
 
 
+def test_device_cached_decoder_cuda_graphs_replay_across_batches():
+    """cuda_graphs=True: the decoder call of every prefix length is captured once and replayed for the next batch
+    of the same shape (other encoder outputs, other lengths, a primer of three tokens); results must equal the
+    eager device-cache path."""
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer
+    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer
+
+    V, beam = 96, 3
+    eos = V - 1
+    # IdentityCTC reads the encoder output as (T, V) log-posteriors, so the decoder's memory width is V here
+    dec = syn.TinyDecoder(V, D=V, seed=6).eval().to(DEV)
+
+    def search(sc):
+        bs = BatchBeamSearch(scorers=dict(decoder=sc, ctc=CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=eos)),
+                             weights=dict(decoder=0.6, ctc=0.4), beam_size=beam, vocab_size=V, sos=eos, eos=eos,
+                             pre_beam_score_key="full")
+        bs.set_hyp_primer([eos, 7, 8])
+        return bs
+
+    graphed, eager = DeviceCachedDecoderScorer(dec, cuda_graphs=True), DeviceCachedDecoderScorer(dec)
+    bs_g, bs_e = search(graphed), search(eager)
+    for batch in range(3):
+        lens = [30, 22 + batch]
+        xs = [syn.random_logp(100 + 10 * batch + i, t, V, scale=2.0).to(DEV) for i, t in enumerate(lens)]
+        a = bs_g.decode_batch(xs, -9, 0.0)
+        b = bs_e.decode_batch(xs, -9, 0.0)
+        for u, v in zip(a, b):
+            assert len(u) == len(v) >= 1
+            for h, r in zip(u, v):
+                assert h.yseq.tolist() == r.yseq.tolist()
+                assert abs(float(h.score) - float(r.score)) <= SCORE_ATOL
+    assert len(graphed._graphs) >= 5  # captured once, replayed by the later batches
+
+
 def test_score_filter_matches_reference_goldens_and_oracle():
     import os
 
