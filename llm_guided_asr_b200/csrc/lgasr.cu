@@ -53,6 +53,7 @@ struct lgasr_handle {
   int ept;           // 8 or 16 elements per selection thread and chunk
   int fused;         // 1: one k_step launch per position; 0: k_score_rows + k_select
   int cluster;       // 1: k_step is launched as clusters of `beam` CTAs (records through distributed shared memory)
+  int seq_ok;        // 1: the whole grid of k_step is one wave, replay positions use the SEQ instance
   std::vector<void*> allocs;
   std::vector<long long> primer;
   std::vector<int> xlens;
@@ -327,6 +328,20 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
         h->cluster = 0;
       }
     }
+    if (e == cudaSuccess) {
+      // the SEQ instance (replay positions) pays only while the whole grid is one wave: its two halves run one
+      // after the other in a CTA, which is hidden by the previous grid's tail at B = 64 (17.9 vs 19.6 us) but
+      // costs slot time once CTAs queue for slots (109.9 vs 92.3 us per launch at B = 512)
+      int per_sm = 0, dev = 0, sms = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_step<false, false, true>, kStepThreads, h->smem_step) !=
+          cudaSuccess) {
+        cudaGetLastError();
+        per_sm = 0;
+      }
+      h->seq_ok = ((long long)per_sm * sms >= (long long)d.B * d.W) ? 1 : 0;
+    }
     if (e == cudaSuccess && h->smem_sel > cur_sel) {
       e = cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_sel);
       if (e == cudaSuccess) cur_sel = h->smem_sel;
@@ -509,7 +524,7 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     // slots of one GPC are free at once, which delays the early start the variant lives on (measured: 20.2 us
     // per launch with clusters, 17.9 us without).
     const char* nseq = getenv("LGASR_NO_SEQ");
-    const bool seq = pdl && !(nseq && nseq[0] == '1');
+    const bool seq = pdl && h->seq_ok && !(nseq && nseq[0] == '1');
     const bool use_cluster = h->cluster && !seq;
     if (use_cluster) {
       at[na].id = cudaLaunchAttributeClusterDimension;
