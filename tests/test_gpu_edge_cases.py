@@ -242,3 +242,12 @@ def test_replay_instances_equal_stepping_on_every_staging_path(monkeypatch, V, n
         eng.replay([mats(i) for i in range(L)], cst, wts, ld=V)
         assert collect() == stepped
     eng.close()
+
+
+@pytest.mark.parametrize("beam,V,T", [(20, 600, 64), (40, 2500, 120), (16, 900, 50), (17, 900, 50)])
+def test_wide_beams(beam, V, T):
+    """Beams above the bench shape: beam 16 is the largest cluster, 17 the first ticket-only width; from beam 20 on
+    the selection sees more than 512 records (rounds of block arg-best instead of rank counting) and the
+    candidates' posterior rows no longer fit one gather group."""
+    nbest, ref = _case(70 + beam, T, V, beam, 9, dict(decoder=0.7, ctc=0.3, lm=0.3, length_bonus=0.1), True, maxr=-14)
+    _check(nbest, ref, n_min=1)
