@@ -244,10 +244,18 @@ def test_replay_instances_equal_stepping_on_every_staging_path(monkeypatch, V, n
     eng.close()
 
 
-@pytest.mark.parametrize("beam,V,T", [(20, 600, 64), (40, 2500, 120), (16, 900, 50), (17, 900, 50)])
+@pytest.mark.parametrize("beam,V,T", [(20, 600, 64), (40, 2500, 120), (16, 900, 50), (17, 900, 50), (85, 3000, 80)])
 def test_wide_beams(beam, V, T):
     """Beams above the bench shape: beam 16 is the largest cluster, 17 the first ticket-only width; from beam 20 on
     the selection sees more than 512 records (rounds of block arg-best instead of rank counting) and the
     candidates' posterior rows no longer fit one gather group."""
     nbest, ref = _case(70 + beam, T, V, beam, 9, dict(decoder=0.7, ctc=0.3, lm=0.3, length_bonus=0.1), True, maxr=-14)
     _check(nbest, ref, n_min=1)
+
+
+def test_pre_beam_wider_than_the_limit_is_refused_loudly():
+    """int(1.5 * 86) + 1 = 130 records per hypothesis exceed LGASR_MAX_PREBEAM: LGASR_EINVAL, no silent fallback."""
+    from llm_guided_asr_b200._lib import LgasrError
+
+    with pytest.raises(LgasrError):
+        _case(99, 40, 3000, 86, 5, dict(decoder=0.7, ctc=0.3), False, maxr=-4)
