@@ -51,68 +51,66 @@ def log_softmax_rows(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -
     return out
 
 
-class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
-    """Full scorer around an attention decoder with the reference's ``BaseTransformerDecoder`` surface
-    (``embed``, ``decoders``, ``after_norm``, ``normalize_before``, ``output_layer``; the layers follow the
-    ``layer(tgt, tgt_mask, memory, memory_mask, cache=c)`` contract of ``forward_one_step``, ``:195-203``).
+class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
+    """Machinery shared by the device-protocol scorers: static buffers per batch shape, one network call per
+    position for all ``B*beam`` row slots (``_net``), ``lgasr_log_softmax_rows`` into the row layout of
+    ``lgasr_step``, ``lgasr_reorder_rows`` of every layer's cache by the parents the step chose, optional CUDA-graph
+    capture of the network call per prefix length."""
 
-    Used by this package's ``BatchBeamSearch`` through the device protocol (``device_begin`` /
-    ``batch_score_padded`` / ``device_reorder``): all ``B*beam`` row slots are scored in one decoder call per
-    position and the caches never leave the device.  Through the plain ``batch_score`` / ``select_state``
-    protocol (e.g. under the reference's own search) it simply delegates to the wrapped decoder.
-    """
-
-    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
+    def __init__(self, net: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
         torch.nn.Module.__init__(self)
-        for name in ("embed", "decoders", "output_layer"):
-            if not hasattr(decoder, name):
-                raise TypeError(f"decoder has no attribute {name!r}: not a BaseTransformerDecoder-like module")
-        self.decoder = decoder
+        self.net = net
         self.fused_log_softmax = fused_log_softmax
-        # cuda_graphs: the decoder call of a position (embed -> layers -> output layer -> log-softmax) is captured
+        # cuda_graphs: the network call of a position (embed -> layers -> output layer -> log-softmax) is captured
         # once per prefix length into a CUDA graph over static buffers and replayed for every later batch of the
-        # same shape: an eager decoder step is ~25 launches per layer, i.e. launch-bound at beam-search sizes
+        # same shape: an eager step is ~25 launches per layer, i.e. launch-bound at beam-search sizes
         self.cuda_graphs = cuda_graphs
         self._eng = None
         self._shape = None
         self._graphs = {}
         self._pool = None
 
-    # ---- plain scorer protocol: delegate ------------------------------------------------------------------
+    # ---- plain scorer protocol: delegate to the wrapped network --------------------------------------------
     def batch_init_state(self, x):
-        return self.decoder.batch_init_state(x) if hasattr(self.decoder, "batch_init_state") else None
+        return self.net.batch_init_state(x) if hasattr(self.net, "batch_init_state") else None
 
     def select_state(self, state, i, new_id=None):
-        return self.decoder.select_state(state, i) if hasattr(self.decoder, "select_state") else state[i]
+        if state is None:
+            return None
+        return self.net.select_state(state, i) if hasattr(self.net, "select_state") else state[i]
 
     def score(self, ys, state, x):
-        return self.decoder.score(ys, state, x)
+        return self.net.score(ys, state, x)
 
     def batch_score(self, ys: torch.Tensor, states: List[Any], xs: torch.Tensor) -> Tuple[torch.Tensor, List[Any]]:
-        return self.decoder.batch_score(ys, states, xs)
+        return self.net.batch_score(ys, states, xs)
 
-    # ---- device protocol ----------------------------------------------------------------------------------
+    # ---- hooks ----------------------------------------------------------------------------------------------
+    def _n_layers(self) -> int:
+        raise NotImplementedError
+
+    def _begin_inputs(self, xs, lens, B, W, T, dev, fresh_shape: bool) -> None:
+        """Per-batch inputs of the network other than the prefixes (static buffers)."""
+
+    def _net(self, tgt: torch.Tensor, cache: List[Optional[torch.Tensor]]):
+        """``tgt (B*W, L)`` int64, per-layer caches ``(B*W, L-1, Dm)`` or None -> ``(logits (B*W, V), new caches)``."""
+        raise NotImplementedError
+
+    # ---- device protocol ------------------------------------------------------------------------------------
     def device_begin(self, xs: Sequence[torch.Tensor], lens: Sequence[int], engine, max_positions: int) -> None:
-        """Start a batch: ``xs[b] (T_b, D)`` encoder outputs; row slot ``b*beam + j`` attends to ``xs[b]``."""
+        """Start a batch: ``xs[b] (T_b, D)`` encoder outputs; row slot ``b*beam + j`` belongs to utterance ``b``."""
         B, W = engine.cfg.n_utts, engine.cfg.beam
         dev = xs[0].device
         T = max(int(t) for t in lens)
         shape = (B, W, T, int(xs[0].shape[-1]), int(max_positions), engine.cfg.vocab, xs[0].dtype, dev)
-        if shape != self._shape:  # static buffers (and the graphs captured over them) live as long as the shape
+        fresh_shape = shape != self._shape
+        if fresh_shape:  # static buffers (and the graphs captured over them) live as long as the shape
             self._shape = shape
             self._graphs, self._pool = {}, None
-            self._memory = xs[0].new_zeros(B * W, T, xs[0].shape[-1])
-            self._memory_mask = torch.zeros(B * W, 1, T, dtype=torch.bool, device=dev)
             self._tgt = torch.zeros(B * W, int(max_positions), dtype=torch.int64, device=dev)
             self._out = torch.empty(B * W, engine.cfg.vocab, dtype=torch.float32, device=dev)
             self._buf = None  # [2] x (n_layers, B*W, cap, Dm), allocated on the first call (Dm known then)
-        mem = self._memory.view(B, W, T, -1)
-        mem.zero_()
-        for b, x in enumerate(xs):
-            mem[b, :, : lens[b]] = x
-        ar = torch.arange(T, device=dev)
-        mask = ar[None, :] < torch.as_tensor(list(lens), device=dev)[:, None]  # (B, T)
-        self._memory_mask.view(B, W, T).copy_(mask[:, None, :].expand(B, W, T))
+        self._begin_inputs(xs, lens, B, W, T, dev, fresh_shape)
         self._eng = engine
         self._cap = int(max_positions)
         self._pp = 0
@@ -121,27 +119,15 @@ class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
         self._V = engine.cfg.vocab
 
     def _forward(self, L: int):
-        """Decoder call for prefix length ``L`` over the static buffers; writes ``self._out``, returns the new
-        per-layer caches ``(B*W, L, Dm)`` (the body of ``forward_one_step``, transformer_decoder.py:195-212,
-        without its log_softmax)."""
-        dec = self.decoder
+        """Network call for prefix length ``L`` over the static buffers; writes ``self._out``, returns the new
+        per-layer caches ``(B*W, L, Dm)``."""
         tgt = self._tgt[:, :L]
-        tgt_mask = torch.ones(L, L, dtype=torch.bool, device=tgt.device).tril().unsqueeze(0)
-        nl = len(dec.decoders)
+        nl = self._n_layers()
         if self._fresh or self._buf is None or L == 1:
             cache = [None] * nl
         else:
             cache = [self._buf[self._pp][i, :, : L - 1] for i in range(nl)]
-        x = dec.embed(tgt)
-        memory, memory_mask = self._memory, self._memory_mask
-        new = []
-        for c, layer in zip(cache, dec.decoders):
-            x, tgt_mask, memory, memory_mask = layer(x, tgt_mask, memory, memory_mask, cache=c)
-            new.append(x)
-        y = x[:, -1]
-        if getattr(dec, "normalize_before", False) and getattr(dec, "after_norm", None) is not None:
-            y = dec.after_norm(y)
-        logits = dec.output_layer(y)
+        logits, new = self._net(tgt, cache)
         if self.fused_log_softmax:
             log_softmax_rows(logits if logits.dtype in (torch.float32, torch.bfloat16) else logits.float(), self._out)
         else:
@@ -191,3 +177,94 @@ class DeviceCachedDecoderScorer(torch.nn.Module, BatchScorerInterface):
         self._pp ^= 1
         self._new = None
         self._fresh = False
+
+
+class DeviceCachedDecoderScorer(_DeviceCachedScorer):
+    """Full scorer around an attention decoder with the reference's ``BaseTransformerDecoder`` surface
+    (``embed``, ``decoders``, ``after_norm``, ``normalize_before``, ``output_layer``; the layers follow the
+    ``layer(tgt, tgt_mask, memory, memory_mask, cache=c)`` contract of ``forward_one_step``,
+    ``espnet2/asr/decoder/transformer_decoder.py:195-203``).
+
+    Used by this package's ``BatchBeamSearch`` through the device protocol (``device_begin`` /
+    ``batch_score_padded`` / ``device_reorder``): all ``B*beam`` row slots are scored in one decoder call per
+    position and the caches never leave the device.  Through the plain ``batch_score`` / ``select_state``
+    protocol (e.g. under the reference's own search) it simply delegates to the wrapped decoder.
+    """
+
+    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
+        for name in ("embed", "decoders", "output_layer"):
+            if not hasattr(decoder, name):
+                raise TypeError(f"decoder has no attribute {name!r}: not a BaseTransformerDecoder-like module")
+        super().__init__(decoder, fused_log_softmax, cuda_graphs)
+
+    @property
+    def decoder(self):
+        return self.net
+
+    def _n_layers(self) -> int:
+        return len(self.net.decoders)
+
+    def _begin_inputs(self, xs, lens, B, W, T, dev, fresh_shape):
+        if fresh_shape:
+            self._memory = xs[0].new_zeros(B * W, T, xs[0].shape[-1])
+            self._memory_mask = torch.zeros(B * W, 1, T, dtype=torch.bool, device=dev)
+        mem = self._memory.view(B, W, T, -1)
+        mem.zero_()
+        for b, x in enumerate(xs):
+            mem[b, :, : lens[b]] = x
+        ar = torch.arange(T, device=dev)
+        mask = ar[None, :] < torch.as_tensor(list(lens), device=dev)[:, None]  # (B, T)
+        self._memory_mask.view(B, W, T).copy_(mask[:, None, :].expand(B, W, T))
+
+    def _net(self, tgt, cache):
+        # the body of forward_one_step (transformer_decoder.py:195-212) without its log_softmax
+        dec = self.net
+        L = tgt.shape[1]
+        tgt_mask = torch.ones(L, L, dtype=torch.bool, device=tgt.device).tril().unsqueeze(0)
+        x = dec.embed(tgt)
+        memory, memory_mask = self._memory, self._memory_mask
+        new = []
+        for c, layer in zip(cache, dec.decoders):
+            x, tgt_mask, memory, memory_mask = layer(x, tgt_mask, memory, memory_mask, cache=c)
+            new.append(x)
+        y = x[:, -1]
+        if getattr(dec, "normalize_before", False) and getattr(dec, "after_norm", None) is not None:
+            y = dec.after_norm(y)
+        return dec.output_layer(y), new
+
+
+class DeviceCachedLMScorer(_DeviceCachedScorer):
+    """Full scorer around a language model with the reference's ``TransformerLM`` surface
+    (``espnet2/lm/transformer_lm.py:12-133``: ``embed``, ``encoder`` with ``embed`` / ``encoders`` /
+    ``normalize_before`` / ``after_norm``, ``decoder``; layers follow ``layer(x, mask, cache=c) -> (x, mask)`` of
+    ``Encoder.forward_one_step``, ``espnet/nets/pytorch_backend/transformer/encoder.py:353-379``).  Replaces the
+    per-hypothesis state transposes of ``TransformerLM.batch_score`` (``:118-122,132``) the same way."""
+
+    def __init__(self, lm: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
+        for name in ("embed", "encoder", "decoder"):
+            if not hasattr(lm, name):
+                raise TypeError(f"language model has no attribute {name!r}: not a TransformerLM-like module")
+        if not hasattr(lm.encoder, "encoders"):
+            raise TypeError("language model encoder has no attribute 'encoders'")
+        super().__init__(lm, fused_log_softmax, cuda_graphs)
+
+    @property
+    def lm(self):
+        return self.net
+
+    def _n_layers(self) -> int:
+        return len(self.net.encoder.encoders)
+
+    def _net(self, tgt, cache):
+        lm, enc = self.net, self.net.encoder
+        L = tgt.shape[1]
+        # _target_mask (:53-56): padding id 0 masked, causal
+        mask = (tgt != 0).unsqueeze(-2) & torch.ones(L, L, dtype=torch.bool, device=tgt.device).tril().unsqueeze(0)
+        xs = enc.embed(lm.embed(tgt))
+        new = []
+        for c, layer in zip(cache, enc.encoders):
+            xs, mask = layer(xs, mask, cache=c)
+            new.append(xs)
+        if getattr(enc, "normalize_before", False):
+            xs = enc.after_norm(xs)
+        return lm.decoder(xs[:, -1]), new

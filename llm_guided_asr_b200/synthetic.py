@@ -215,3 +215,85 @@ class TinyDecoder(torch.nn.Module, BatchScorerInterface):
         mask = torch.ones(L, L, dtype=torch.bool, device=ys.device).tril().unsqueeze(0)
         logp, st = self.forward_one_step(ys, mask, xs, cache=cache)
         return logp, [[st[i][b] for i in range(nl)] for b in range(n)]
+
+
+class _TinyLMLayer(torch.nn.Module):
+    """Pre-norm self-attention layer with the call contract of the reference's ``EncoderLayer``
+    (``espnet/nets/pytorch_backend/transformer/encoder_layer.py``): ``layer(x, mask, cache=None) -> (x, mask)``;
+    with ``cache (n, L-1, D)`` only the last position is computed and appended."""
+
+    def __init__(self, D: int, heads: int, ff: int):
+        super().__init__()
+        self.H = heads
+        self.n1, self.n2 = torch.nn.LayerNorm(D), torch.nn.LayerNorm(D)
+        self.q, self.kv, self.o = torch.nn.Linear(D, D), torch.nn.Linear(D, 2 * D), torch.nn.Linear(D, D)
+        self.f1, self.f2 = torch.nn.Linear(D, ff), torch.nn.Linear(ff, D)
+
+    def forward(self, x, mask, cache=None):
+        y = self.n1(x)
+        if cache is None:
+            q_in, res, m1 = y, x, mask
+        else:
+            q_in, res = y[:, -1:], x[:, -1:]
+            m1 = None if mask is None else mask[:, -1:]
+        n, Lq, D = q_in.shape
+        k, v = self.kv(y).chunk(2, dim=-1)
+        sp = lambda t: t.view(n, t.shape[1], self.H, D // self.H).transpose(1, 2)  # noqa: E731
+        a = torch.matmul(sp(self.q(q_in)), sp(k).transpose(-1, -2)) / float(D // self.H) ** 0.5
+        if m1 is not None:
+            a = a.masked_fill(~m1.unsqueeze(1), float("-inf"))
+        att = torch.matmul(torch.softmax(a, dim=-1), sp(v)).transpose(1, 2).reshape(n, Lq, D)
+        h = res + self.o(att)
+        h = h + self.f2(torch.relu(self.f1(self.n2(h))))
+        if cache is not None:
+            h = torch.cat([cache, h], dim=1)
+        return h, mask
+
+
+class _TinyLMEncoder(torch.nn.Module):
+    def __init__(self, E: int, D: int, layers: int, heads: int, ff: int):
+        super().__init__()
+        self.embed = torch.nn.Linear(E, D)  # input_layer="linear" of the reference's Encoder
+        self.encoders = torch.nn.ModuleList([_TinyLMLayer(D, heads, ff) for _ in range(layers)])
+        self.after_norm = torch.nn.LayerNorm(D)
+        self.normalize_before = True
+
+    def forward_one_step(self, xs, masks, *, cache=None):
+        xs = self.embed(xs)
+        if cache is None:
+            cache = [None] * len(self.encoders)
+        new_cache = []
+        for c, e in zip(cache, self.encoders):
+            xs, masks = e(xs, masks, cache=c)
+            new_cache.append(xs)
+        return self.after_norm(xs), masks, new_cache
+
+
+class TinyLM(torch.nn.Module, BatchScorerInterface):
+    """Small random-init language model with the attribute and method surface of the reference's
+    ``TransformerLM`` (``espnet2/lm/transformer_lm.py:12-133``: ``embed``, ``encoder``, ``decoder``, ``_target_mask``,
+    ``score``, ``batch_score`` with per-hypothesis lists of per-layer states)."""
+
+    def __init__(self, V: int, E: int = 16, D: int = 32, layers: int = 2, heads: int = 4, ff: int = 64, seed: int = 0):
+        torch.nn.Module.__init__(self)
+        with torch.random.fork_rng(devices=[]):
+            torch.manual_seed(seed)
+            self.embed = torch.nn.Embedding(V, E)
+            self.encoder = _TinyLMEncoder(E, D, layers, heads, ff)
+            self.decoder = torch.nn.Linear(D, V)
+
+    def _target_mask(self, ys):
+        L = ys.shape[-1]
+        return (ys != 0).unsqueeze(-2) & torch.ones(L, L, dtype=torch.bool, device=ys.device).tril().unsqueeze(0)
+
+    def score(self, y, state, x):
+        y = y.unsqueeze(0)
+        h, _, cache = self.encoder.forward_one_step(self.embed(y), self._target_mask(y), cache=state)
+        return self.decoder(h[:, -1]).log_softmax(dim=-1).squeeze(0), cache
+
+    def batch_score(self, ys, states, xs):
+        n, nl = len(ys), len(self.encoder.encoders)
+        cache = None if states[0] is None else [torch.stack([states[b][i] for b in range(n)]) for i in range(nl)]
+        h, _, st = self.encoder.forward_one_step(self.embed(ys), self._target_mask(ys), cache=cache)
+        logp = self.decoder(h[:, -1]).log_softmax(dim=-1)
+        return logp, [[st[i][b] for i in range(nl)] for b in range(n)]

@@ -195,6 +195,40 @@ def test_device_cached_decoder_cuda_graphs_replay_across_batches():
     assert len(graphed._graphs) >= 5  # captured once, replayed by the later batches
 
 
+@pytest.mark.parametrize("graphs", [False, True])
+def test_device_cached_decoder_and_lm_together(graphs):
+    """Decoder and language model both behind the device protocol (two cached scorers, two fused terms) against
+    the same search with the reference's host-side state protocol; two batches, the second replays graphs."""
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer
+    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer, DeviceCachedLMScorer
+
+    V, beam = 80, 4
+    eos = V - 1
+    dec = syn.TinyDecoder(V, D=V, seed=8).eval().to(DEV)
+    lm = syn.TinyLM(V, seed=9).eval().to(DEV)
+    weights = dict(decoder=0.6, ctc=0.4, lm=0.5)
+
+    def search(d, m):
+        return BatchBeamSearch(scorers=dict(decoder=d, ctc=CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=eos), lm=m),
+                               weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
+
+    dev_bs = search(DeviceCachedDecoderScorer(dec, cuda_graphs=graphs), DeviceCachedLMScorer(lm, cuda_graphs=graphs))
+    host_bs = search(dec, lm)
+    for batch in range(2):
+        lens = [26, 33, 19]
+        xs = [syn.random_logp(200 + 10 * batch + i, t, V, scale=2.0).to(DEV) for i, t in enumerate(lens)]
+        a = dev_bs.decode_batch(xs, -10, 0.0)
+        b = host_bs.decode_batch(xs, -10, 0.0)
+        for u, v in zip(a, b):
+            assert len(u) == len(v) >= 1
+            for h, r in zip(u, v):
+                assert h.yseq.tolist() == r.yseq.tolist()
+                assert abs(float(h.score) - float(r.score)) <= SCORE_ATOL
+                for k in ("decoder", "lm", "ctc"):
+                    assert abs(float(h.scores[k]) - float(r.scores[k])) <= SCORE_ATOL
+
+
 def test_score_filter_matches_reference_goldens_and_oracle():
     import os
 
