@@ -16,7 +16,13 @@
 //                         memory; log psi = logsumexp_t(phi[t-1] + x[t,c]) (+) r^n_{start-1} per warp
 //                         (ctc_prefix_score.py:163-185), then w_ctc*(psi - s_prev) + fused + running score
 //                         (batch_beam_search.py:313-318) -> candidate records.
-//   last CTA of an utterance to finish (atomic ticket): utt_select = global top-beam + bookkeeping.
+//   record exchange: through rank 0's shared memory when the `beam` CTAs of an utterance run as one
+//                         thread-block cluster (CL), else through L2 with an atomic ticket; the receiving CTA
+//                         runs utt_select = global top-beam + bookkeeping.
+//
+//   Instances k_step<TR, CL, SEQ>: TR adds clock64/globaltimer stamps (LGASR_TRACE=1); SEQ is the instance of
+//   programmatic dependent launches inside a replay: the sel work runs on all eight warps BEFORE
+//   griddepcontrol.wait (it depends only on inputs of the step), the ctc work on four warps after it.
 #pragma once
 #include "lgasr_kernels.cuh"
 
