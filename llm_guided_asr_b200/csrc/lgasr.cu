@@ -173,8 +173,44 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     const int K = d.K > 0 ? d.K : 1;
     // stage budget: 6144 floats (24 KB).  A row set that fits is ONE chunk; longer rows are streamed through
     // two stages of half the budget each.
-    const int budget = 6144;
+    int budget = 6144;
     const int V4 = (d.V + 3) & ~3;
+    const char* ncl0 = getenv("LGASR_NO_CLUSTER");
+    const bool want_cluster = h->fused && d.W >= 2 && d.W <= 16 && !(ncl0 && ncl0[0] == '1');
+    const long long selw0 = utt_select_smem_floats(d.W, d.R, d.NS);
+    // dynamic shared memory of a CTA for a given ring budget (the arena also holds the candidate rows and, in the
+    // ticket instance, the selection's working set)
+    auto total_for = [&](int bud) -> long long {
+      long long ar = ((long long)K * V4 <= bud) ? (long long)K * V4 : 2LL * K * ((bud / (2 * K)) & ~3);
+      long long cd = (long long)n_sel * d.Tp;
+      if (cd > 6144) cd = 6144;
+      if (cd < d.Tp) cd = d.Tp;
+      if (d.mode == kModePreBeam && cd > ar) ar = cd;
+      if (selw0 > ar) ar = selw0;
+      ar = (ar + 3) & ~3LL;
+      return (long long)sizeof(StepSmem) + 6LL * d.Tp * sizeof(float) + ar * (long long)sizeof(float) +
+             (want_cluster ? selw0 * (long long)sizeof(float) : 0);
+    };
+    if ((long long)K * V4 > budget) {
+      // a streamed row set: if the default ring is what pushes the CTA over the five-per-SM footprint AND that
+      // turns a one-wave grid into two (two full scorers at configs[1] size: 45.4 KB -> four CTAs per SM -> the
+      // 640 CTAs no longer fit, 37 us per launch instead of 24), shrink the ring by the few hundred bytes it
+      // takes to stay at five.  Otherwise the larger chunks win (OWSM shape: 29 vs 36 us).
+      const long long per_cta5 = (227LL * 1024) / 5 - 1024 - 512;  // 1 KB reserved per CTA + static shared memory
+      int dev = 0, sms = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const long long tot0 = total_for(budget);
+      const long long per_sm0 = (227LL * 1024) / (tot0 + 1024 + 512);
+      const long long ctas = (long long)d.B * d.W;
+      if (tot0 > per_cta5 && ctas > per_sm0 * sms && ctas <= 5LL * sms) {
+        const long long fixed = tot0 - ((tot0 - (long long)sizeof(StepSmem) - 6LL * d.Tp * sizeof(float) -
+                                         (want_cluster ? selw0 * (long long)sizeof(float) : 0)));
+        const long long room = (per_cta5 - fixed) / (long long)sizeof(float);
+        if (room < budget && room >= 4096 && ((room / (2 * K)) & ~3LL) >= 256 && total_for((int)room) <= per_cta5)
+          budget = (int)room;
+      }
+    }
     int nst = 1;
     if ((long long)K * V4 <= budget) {
       sl.CH = V4;
