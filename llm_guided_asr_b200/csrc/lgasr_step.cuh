@@ -513,6 +513,22 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
           fz[q] = v;
           mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
         }
+      } else if ((key < 0) && (tm.K == 2) && (tm.nptr == 2) && ((n_ch & 3) == 0)) {
+        // two matrices (decoder + LM/LLM): (0 + w0*s0) + w1*s1, the first sum being exact
+        const float w0 = tm.w[0], w1 = tm.w[1];
+        const float4* f1 = reinterpret_cast<const float4*>(sb + tm.slot[1] * CH);
+        const float4* f0 = reinterpret_cast<const float4*>(sb + tm.slot[0] * CH);
+#pragma unroll 2
+        for (int q = j; q < nq; q += NSG) {
+          const float4 a = f0[q], b2 = f1[q];
+          float4 v;
+          v.x = __fadd_rn(__fmul_rn(w0, a.x), __fmul_rn(w1, b2.x));
+          v.y = __fadd_rn(__fmul_rn(w0, a.y), __fmul_rn(w1, b2.y));
+          v.z = __fadd_rn(__fmul_rn(w0, a.z), __fmul_rn(w1, b2.z));
+          v.w = __fadd_rn(__fmul_rn(w0, a.w), __fmul_rn(w1, b2.w));
+          fz[q] = v;
+          mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+        }
       } else
 #pragma unroll 1
       for (int q = j; q < nq; q += NSG) {
