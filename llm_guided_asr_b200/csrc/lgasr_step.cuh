@@ -611,6 +611,9 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
             }
           }
         };
+        // a thread whose own maximum of sweep 1 is below the threshold has nothing to push: on the chunks after
+        // the list has filled (long rows) almost every thread skips the second pass over shared memory
+        if (mx >= thr_v)
 #pragma unroll 1
         for (int q = j; q < nq; q += NSG) {
           const float4 v = fz[q];
