@@ -152,22 +152,64 @@ def cpu_oracle_run(logp, tables, cfg, utts, procs):
     return time.perf_counter() - t0, res
 
 
+def _quiet_reference_logs():
+    import logging
+
+    for name in ("espnet.nets.beam_search", "espnet.nets.batch_beam_search", "root"):
+        logging.getLogger(name if name != "root" else None).setLevel(logging.ERROR)
+
+
+def make_inputs_subset(cfg, utts, positions, rank=0):
+    """The same numbers as make_inputs(rank, cfg) for utterances `utts` and the first `positions` positions only
+    (every utterance / position has its own seed, the position matrices always have all B*beam rows)."""
+    B, T, V, W = cfg["B"], cfg["T"], cfg["V"], cfg["beam"]
+    logp = {}
+    for b in utts:
+        g = torch.Generator().manual_seed(7 + 1000 * rank + b)
+        logp[b] = torch.log_softmax(3.0 * torch.randn(T, V, generator=g), dim=-1)
+    tables = torch.empty(positions, B * W, V)
+    for i in range(positions):
+        g = torch.Generator().manual_seed(11 + i + 100000 * rank)
+        tables[i] = torch.log_softmax(2.0 * torch.randn(B * W, V, generator=g), dim=-1)
+    return logp, tables
+
+
+def reference_cpu_run(logp, tables, cfg, utts, positions, procs):
+    """The UNMODIFIED reference (baseline/_ref: BatchBeamSearch + CTCPrefixScorer/CTCPrefixScoreTH, table decoder) on
+    the host cores, one single-threaded process per utterance (inference_nj sharding, egs2/*/asr.sh:1555-1585).
+    Falls back to the numpy oracle port when baseline/_ref is absent.  Returns (seconds, results, kind)."""
+    from baseline import ref_harness as rh
+
+    if rh.available():
+        rh.activate()
+        _quiet_reference_logs()
+        dt, res = rh.decode_many_cpu(logp, tables, cfg, utts, positions, procs)
+        return dt, res, "reference"
+    dt, res = cpu_oracle_run(logp, tables, dict(cfg, L=positions), utts, procs)
+    return dt, res, "port"
+
+
 def run_reference(args, rank, world):
+    """Reference arm: the reference's own CPU implementation of the path on the box's host cores, same config,
+    metric and inputs (utterances 0..cores-1 of the GPU arm's batch, all 64 positions) as the GPU arm."""
     if rank != 0:
         return
     torch.set_num_threads(1)
     cores = os.cpu_count() or 1
     cfg = dict(CFG)
-    logp, tables = make_inputs(0, dict(cfg, B=min(cfg["B"], max(cores, 2))))
-    n_utts = min(logp.shape[0], cores)
-    times = []
+    n_utts = min(cfg["B"], cores)
+    utts = list(range(n_utts))
+    lp, tables = make_inputs_subset(cfg, utts, cfg["L"])
+    logp = torch.stack([lp[b] for b in utts])
+    times, kind = [], "port"
     for i in range(args.warmup + args.steps):
-        # bounded sample per step: one utterance per core, the same 64-position decode
-        dt, _ = cpu_oracle_run(logp, tables, cfg, list(range(n_utts)), cores)
+        dt, _, kind = reference_cpu_run(logp, tables, cfg, utts, cfg["L"], cores)
         if i >= args.warmup:
             times.append(dt)
     per_step = sum(times) / len(times)
     value = n_utts / per_step
+    what = ("unmodified reference classes from baseline/_ref (BatchBeamSearch + CTCPrefixScoreTH, torch CPU fp32)"
+            if kind == "reference" else "numpy oracle port (baseline/_ref not installed)")
     line = {
         "impl": "reference",
         "metric": "decode_utts_per_sec",
@@ -185,13 +227,47 @@ def run_reference(args, rank, world):
         "config": bench_config(cfg),
         "rtfx": value * AUDIO_SEC,
         "cpu_baseline": {
-            "value": value, "unit": "utts/s", "cores": cores, "kind": "port",
-            "sample": f"{n_utts} utterances x {cfg['L']} positions per step, one process per core (numpy oracle port of CTCPrefixScoreTH + BatchBeamSearch)",
+            "value": value, "unit": "utts/s", "cores": cores, "kind": kind,
+            "sample": f"utterances 0..{n_utts - 1} of the GPU arm's batch x {cfg['L']} positions per step, one single-threaded process per core: {what}",
         },
         "e2e": {"value": value, "unit": "utts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def run_reference_gpu(args):
+    """The north_star's 20x denominator: the reference's own GPU PyTorch BatchBeamSearch (same classes on cuda:0), one
+    utterance at a time as the reference requires (asr_inference.py:759-764), median of >= 5 utterances after one
+    warm-up utterance, torch.cuda.synchronize() on both sides.  Prints one JSON line."""
+    from baseline import ref_harness as rh
+
+    if not rh.available():
+        print(json.dumps({"impl": "reference_gpu", "unavailable": "baseline/_ref not installed (scripts/install_ref.sh)"}))
+        return
+    rh.activate()
+    _quiet_reference_logs()
+    cfg = dict(CFG)
+    n = max(5, min(args.steps, 8))
+    utts = list(range(n + 1))
+    lp, tables = make_inputs_subset(cfg, utts, cfg["L"])
+    dev = "cuda:0"
+    W = cfg["beam"]
+    d_tables = tables.to(dev)
+    times, results = [], []
+    for b in utts:
+        dt, nb = rh.decode_one(lp[b], d_tables[:, b * W : (b + 1) * W], cfg, cfg["L"], device=dev)
+        if b > 0:
+            times.append(dt)
+        results.append(nb[0])
+    med = statistics.median(times)
+    print(json.dumps({
+        "impl": "reference_gpu", "metric": "decode_utts_per_sec", "value": 1.0 / med, "unit": "utts/s",
+        "sec_per_utt_median": med, "sec_per_utt_all": times, "ms_per_position": med * 1e3 / cfg["L"],
+        "utts": n, "positions": cfg["L"], "device": torch.cuda.get_device_name(0),
+        "what": "unmodified reference BatchBeamSearch + CTCPrefixScoreTH on cuda:0 (torch eager fp32), one utterance at a time, table decoder resident on the device",
+        "best": [[r[0], r[1]] for r in results],
+    }), flush=True)
 
 
 def bench_config(cfg):
@@ -393,7 +469,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference_gpu"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -401,6 +477,10 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.impl == "reference_gpu":
+        if rank == 0:
+            run_reference_gpu(args)
         return
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

@@ -14,6 +14,7 @@
 #include "lgasr_kernels.cuh"
 #include "lgasr_scorer_kernels.cuh"
 #include "lgasr_step.cuh"
+#include "lgasr_step2.cuh"
 #include "lgasr_state_kernels.cuh"
 
 using namespace lgasr;
@@ -54,6 +55,10 @@ struct lgasr_handle {
   int fused;         // 1: one k_step launch per position; 0: k_score_rows + k_select
   int cluster;       // 1: k_step is launched as clusters of `beam` CTAs (records through distributed shared memory)
   int seq_ok;        // 1: the whole grid of k_step is one wave, replay positions use the SEQ instance
+  int v2;            // 1: k_step2 (second-generation step kernel) runs the position; 0: k_step (LGASR_V1=1)
+  StepLaunch sl2;    // k_step2 launch geometry
+  size_t smem_step2;
+  int cluster2;      // k_step2 launched as clusters of `beam` CTAs
   std::vector<void*> allocs;
   std::vector<long long> primer;
   std::vector<int> xlens;
@@ -144,10 +149,14 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
   d.Ecap = c->beam * c->max_len_cap;
   d.end_detect = c->end_detect ? 1 : 0;
   d.NS = d.K + d.use_ctc;
+  d.P = c->primer_len;
   d.d_end = -10.0;  // float(np.log(1 * np.exp(-10))) == -10.0 exactly, e2e_asr_common.py:17
   // do_pre_beam rule of beam_search.py:115-119
   const bool do_pre_beam = d.use_ctc && d.key != -2 && d.S < d.V;
   d.mode = !d.use_ctc ? kModeNoCtc : (do_pre_beam ? kModePreBeam : kModeFullCtc);
+  // the pre-beam key only exists while there is a pre-beam: without a partial scorer the reference ranks the full
+  // weighted sum whatever pre_beam_score_key says (do_pre_beam False, beam_search.py:115-119; batch_beam_search.py:302-308)
+  if (d.mode != kModePreBeam) d.key = -1;
   if (d.mode == kModePreBeam && d.S < 1) return fail(LGASR_EINVAL, "pre_beam must be >= 1");
   const int n_sel = d.mode == kModePreBeam ? d.S : d.W;
   if (n_sel > LGASR_MAX_PREBEAM) {
@@ -387,6 +396,69 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       return fail(LGASR_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     }
   }
+  // ---- k_step2 geometry: 6 scan rows of Tp + 4 floats, arena = pending keys | candidate rows | selection scratch ----
+  {
+    const char* v2 = getenv("LGASR_V2");  // work in progress: k_step2 is opt-in until it beats k_step
+    h->v2 = h->fused && (v2 && v2[0] == '1');
+    if (h->v2) {
+      StepLaunch& sl = h->sl2;
+      sl = h->sl;
+      const long long selw = utt_select_smem_floats(d.W, d.R, d.NS);
+      long long arena = (long long)n_sel * d.Tp;
+      if (arena > 6144) arena = 6144;
+      if (arena < d.Tp) arena = d.Tp;
+      if (d.mode != kModePreBeam) arena = 0;
+      if (arena < 2 * kPend2) arena = 2 * kPend2;
+      if (selw > arena) arena = selw;
+      arena = (arena + 3) & ~3LL;
+      sl.arena_floats = (int)arena;
+      int rpg = (int)(arena / d.Tp);
+      if (rpg < 1) rpg = 1;
+      if (rpg > n_sel) rpg = n_sel;
+      sl.rows_per_group = rpg;
+      const char* ncl = getenv("LGASR_NO_CLUSTER");
+      h->cluster2 = d.W >= 2 && d.W <= 16 && !(ncl && ncl[0] == '1');
+      const size_t base = sizeof(Step2Smem) + (size_t)6 * (d.Tp + 4) * sizeof(float) + (size_t)arena * sizeof(float);
+      h->smem_step2 = base + (h->cluster2 ? (size_t)selw * sizeof(float) : 0);
+      if (h->smem_step2 > 220 * 1024) {
+        lgasr_destroy(h);
+        return fail(LGASR_EINVAL, "shared memory need too large for the fused step (T=%d beam=%d)", d.T, d.W);
+      }
+      // the attributes are per device: set them for every handle (cheap) instead of tracking high-water marks
+      cudaError_t e = cudaSuccess;
+      const void* fns[6] = {(const void*)k_step2<false, 0>, (const void*)k_step2<false, 1>, (const void*)k_step2<false, 2>,
+                            (const void*)k_step2<true, 0>,  (const void*)k_step2<true, 1>,  (const void*)k_step2<true, 2>};
+      for (int i = 0; i < 6 && e == cudaSuccess; ++i)
+        e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step2);
+      if (e == cudaSuccess && h->cluster2) {
+        for (int i = 3; i < 6 && e == cudaSuccess; ++i)
+          e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        int ncl_max = 0;
+        cudaLaunchConfig_t qc = {};
+        qc.gridDim = dim3(d.W, d.B);
+        qc.blockDim = dim3(kStepThreads);
+        qc.dynamicSmemBytes = h->smem_step2;
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = d.W;
+        qa[0].val.clusterDim.y = 1;
+        qa[0].val.clusterDim.z = 1;
+        qc.attrs = qa;
+        qc.numAttrs = 1;
+        // clusters only pay while every utterance's cluster is resident at once (one wave)
+        if (e != cudaSuccess || cudaOccupancyMaxActiveClusters(&ncl_max, k_step2<true, 1>, &qc) != cudaSuccess || ncl_max < d.B) {
+          cudaGetLastError();
+          e = cudaSuccess;
+          h->cluster2 = 0;
+          h->smem_step2 = base;
+        }
+      }
+      if (e != cudaSuccess) {
+        lgasr_destroy(h);
+        return fail(LGASR_ECUDA, "cudaFuncSetAttribute(k_step2): %s", cudaGetErrorString(e));
+      }
+    }
+  }
   *out = h;
   return LGASR_OK;
 }
@@ -534,7 +606,62 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     }
     CK(cudaEventRecord(pe[0], st));
   }
-  if (h->fused) {
+  // k_step2 reads the rows with 16-byte loads: aligned rows whose length is a multiple of 4 entries (anything else,
+  // fp32 only, takes k_step, which can stage unaligned rows with plain loads)
+  bool al = (tm.ld % 4 == 0) && (d.V % 4 == 0), plain = true;
+  for (int k = 0; k < tm.K; ++k)
+    if (tm.ptr[k]) {
+      al = al && ((reinterpret_cast<uintptr_t>(tm.ptr[k]) & 15) == 0);
+      plain = plain && !tm.bf16[k] && !tm.norm[k];
+    }
+  if (!plain && !(h->v2 && al))
+    return fail(LGASR_EINVAL, "bf16 / normalised term matrices need 16-byte aligned rows, V %% 4 == 0 and the fused step");
+  if (!plain && d.key >= 0 && (tm.bf16[d.key] || tm.norm[d.key]))
+    return fail(LGASR_EINVAL, "the pre-beam key term must be a plain fp32 log-probability matrix");
+  if (h->v2 && al) {
+    StepLaunch sl = h->sl2;
+    sl.tma_rows = 1;
+    sl.row_path = (d.key >= 0) ? 1 : (plain && tm.K == 1 && tm.nptr == 1) ? 1 : (plain && tm.K == 2 && tm.nptr == 2) ? 2 : 0;
+    sl.pdl = pdl ? 1 : 0;
+    sl.flags = 0;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kStepThreads);
+    cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (pdl) {
+      at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
+    // replay positions (programmatic launches) run as single CTAs with the ticket hand-off: clusters of `beam` CTAs
+    // only become resident when `beam` slots of one GPC are free at once, which delays the early start they live on
+    const char* pcl = getenv("LGASR_PDL_CLUSTER");
+    const bool use_cluster = h->cluster2 && (!pdl || (pcl && pcl[0] == '1'));
+    if (use_cluster) {
+      at[na].id = cudaLaunchAttributeClusterDimension;
+      at[na].val.clusterDim.x = d.W;
+      at[na].val.clusterDim.y = 1;
+      at[na].val.clusterDim.z = 1;
+      ++na;
+    }
+    cfg.attrs = at;
+    cfg.numAttrs = na;
+    // without the cluster the selection scratch aliases the arena: the extra buffer is not needed
+    cfg.dynamicSmemBytes = h->smem_step2;
+    auto kern = k_step2<false, 0>;
+    if (use_cluster)
+      kern = sl.row_path == 1 ? k_step2<true, 1> : sl.row_path == 2 ? k_step2<true, 2> : k_step2<true, 0>;
+    else
+      kern = sl.row_path == 1 ? k_step2<false, 1> : sl.row_path == 2 ? k_step2<false, 2> : k_step2<false, 0>;
+    CK(cudaLaunchKernelEx(&cfg, kern, d, tm, sl, h->pp, h->rp, h->step));
+    LAUNCH_CK();
+    if (h->profiling) {
+      CK(cudaEventRecord(pe[1], st));
+      CK(cudaEventRecord(pe[2], st));
+    }
+  } else if (h->fused) {
     StepLaunch sl = h->sl;
     // TMA bulk copies need 16-byte aligned rows whose chunks are multiples of 16 bytes
     bool al = (tm.nptr > 0) && (tm.ld % 4 == 0) && (d.V % 4 == 0);
@@ -617,8 +744,8 @@ extern "C" int lgasr_step(lgasr_handle* h, const float* const* h_term_ptr, const
 
 extern "C" int lgasr_launch_info(lgasr_handle* h, int32_t* cluster, int32_t* smem_bytes, int32_t* chunk_floats, int32_t* stages) {
   if (!h) return fail(LGASR_EINVAL, "null handle");
-  if (cluster) *cluster = h->fused ? h->cluster : 0;
-  if (smem_bytes) *smem_bytes = (int32_t)(h->fused ? h->smem_step : h->smem_rows);
+  if (cluster) *cluster = h->v2 ? h->cluster2 : (h->fused ? h->cluster : 0);
+  if (smem_bytes) *smem_bytes = (int32_t)(h->v2 ? h->smem_step2 : (h->fused ? h->smem_step : h->smem_rows));
   if (chunk_floats) *chunk_floats = h->sl.CH;
   if (stages) *stages = h->sl.NST;
   return LGASR_OK;

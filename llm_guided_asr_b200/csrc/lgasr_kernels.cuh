@@ -20,10 +20,12 @@ constexpr int kRowWarps = kRowThreads / 32;
 constexpr int kSelThreads = 256;
 
 struct Terms {
-  const float* ptr[kMaxTerms];
+  const float* ptr[kMaxTerms];   // (B*beam, ld) matrix of term k (fp32, or bf16 when bf16[k]); NULL: constant term
+  const float* norm[kMaxTerms];  // optional per-row normaliser: log-probability = entry - norm[row] (logits + logsumexp)
   float cst[kMaxTerms];
   float w[kMaxTerms];
   int slot[kMaxTerms];  // index of term k among the terms that have a matrix (staging order)
+  unsigned char bf16[kMaxTerms];
   int nptr;             // number of terms with a matrix
   int K;
   long long ld;
@@ -31,6 +33,7 @@ struct Terms {
 
 struct Dev {
   int B, T, Tp, V, W, S, R, K, key, use_ctc, mode, blank, sos, eos, Lcap, Ecap, maxlen_cap, end_detect, NS;
+  int P;  // primer length: decode position of an utterance = cur_len - P
   float w_ctc;
   double d_end;
   const float* xT;  // [B][V][Tp]
@@ -69,6 +72,19 @@ struct Dev {
 constexpr int kModePreBeam = 0;  // CTC with pre-beam: S candidates + eos per hypothesis
 constexpr int kModeNoCtc = 1;    // full scorers only: top-beam per hypothesis
 constexpr int kModeFullCtc = 2;  // CTC over the whole vocabulary (ctc_weight == 1.0 / tiny V)
+
+// one full-scorer entry: fp32 or bf16 storage, optional per-row normaliser (log-probability = logit - logsumexp)
+__device__ __forceinline__ float term_at(const Terms& t, int k, int row, long long rowoff, int v) {
+  float s;
+  if (t.bf16[k]) {
+    const unsigned short u = __ldg(reinterpret_cast<const unsigned short*>(t.ptr[k]) + rowoff + v);
+    s = __uint_as_float((unsigned)u << 16);
+  } else {
+    s = __ldg(t.ptr[k] + rowoff + v);
+  }
+  if (t.norm[k]) s = __fsub_rn(s, __ldg(t.norm[k] + row));
+  return s;
+}
 
 // sum_k w_k * s_k[v] in the reference's fp32 order: ((0 + w0*s0) + w1*s1) + ...  (no FMA contraction)
 __device__ __forceinline__ float fuse_at(const Terms& t, long long rowoff, int v) {
@@ -673,7 +689,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
       const float* sc_in = p_scores + h * NS;
       const long long rowoff = (long long)prow * tm.ld;
       for (int k = 0; k < tm.K; ++k) {
-        const float s = tm.ptr[k] ? __ldg(tm.ptr[k] + rowoff + tok) : tm.cst[k];
+        const float s = tm.ptr[k] ? term_at(tm, k, prow, rowoff, tok) : tm.cst[k];
         sc_out[k] = __fadd_rn(sc_in[k], s);
       }
       if (d.use_ctc) sc_out[tm.K] = __fadd_rn(sc_in[tm.K], __fsub_rn(psi, p_sprev[h]));

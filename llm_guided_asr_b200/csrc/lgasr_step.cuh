@@ -47,6 +47,7 @@ struct StepLaunch {
   int tma_rows;        // 1: full-scorer rows are 16-byte aligned -> bulk copies; 0: plain loads
   int arena_floats;    // union buffer: row stages | candidate rows | selection scratch
   int rows_per_group;  // candidate rows that fit the arena
+  int row_path;        // k_step2: 1 = one fp32 matrix (or the key term), 2 = two fp32 matrices, 0 = general term loop
 };
 
 // ---- mbarrier / bulk-copy PTX -----------------------------------------------------------------------

@@ -55,6 +55,10 @@ CASES = [
     dict(name="primer", kind="peaky", T=72, V=90, beam=4, ctc=0.3, lm=0.0, pen=0.0, maxr=0.0, minr=0.0, ntok=10, primer=[88, 5, 7]),
     dict(name="tiny_T", kind="random", T=3, V=20, beam=3, ctc=0.3, lm=0.0, pen=0.0, maxr=0.0, minr=0.0),
     dict(name="mid_vocab", kind="random", T=96, V=1000, beam=10, ctc=0.3, lm=0.5, pen=0.0, maxr=-16, minr=0.0),
+    # round 2: no CTC scorer + pre_beam_score_key="decoder" + LM: do_pre_beam is False without a partial scorer
+    # (beam_search.py:115-119), so the key must be ignored and the top-k taken over the full weighted sum
+    dict(name="no_ctc_key_decoder", kind="peaky", T=60, V=80, beam=5, ctc=0.0, lm=0.5, pen=0.1, maxr=0.0, minr=0.0, ntok=10, key="decoder"),
+    dict(name="no_ctc_key_random", kind="random", T=40, V=120, beam=6, ctc=0.0, lm=0.7, pen=0.0, maxr=-14, minr=0.0, key="decoder"),
 ]
 
 
@@ -184,7 +188,10 @@ def run_case(c, seed):
 
 
 def main():
+    only = set(sys.argv[1:])  # optional: regenerate only the named cases
     for idx, c in enumerate(CASES):
+        if only and c["name"] not in only:
+            continue
         seed = 1000 + 17 * idx
         out = run_case(c, seed)
         path = os.path.join(HERE, c["name"] + ".npz")
