@@ -16,6 +16,7 @@ kernels behind the C ABI (``include/lgasr.h``), with one small D2H read per posi
 There is no CPU path: construction works anywhere, decoding needs the CUDA library and a GPU.
 """
 
+from collections import OrderedDict
 from typing import Any, Dict, List, NamedTuple, Optional, Sequence, Union
 
 import torch
@@ -116,7 +117,7 @@ class BatchBeamSearch(torch.nn.Module):
         )
         self.return_hs = return_hs
         self.normalize_length = normalize_length
-        self._engines: Dict[tuple, FusedStepEngine] = {}
+        self._engines: "OrderedDict[tuple, FusedStepEngine]" = OrderedDict()
         self.last_steps = 0  # decode positions executed by the last call
 
     def set_hyp_primer(self, hyp_primer: List[int] = None) -> None:
@@ -124,12 +125,20 @@ class BatchBeamSearch(torch.nn.Module):
 
     # ------------------------------------------------------------------------------------------
     def _engine(self, B, T, maxcap, primer_len, end_detect, device) -> FusedStepEngine:
-        key = (B, T, maxcap, primer_len, end_detect, str(device))
+        """Device workspace for a batch: cached on BUCKETED capacities (frames and positions rounded up to 64), so
+        that utterances of similar length reuse one handle (per-utterance ``xlens`` / ``maxlen`` go to
+        ``set_posteriors`` / ``begin``); least-recently-used eviction."""
+        Tcap = -(-T // 64) * 64
+        Lcap = -(-maxcap // 64) * 64
+        key = (B, Tcap, Lcap, primer_len, end_detect, str(device))
         eng = self._engines.get(key)
-        if eng is None:
-            if len(self._engines) >= 4:  # bounded cache of device workspaces
-                _, old = self._engines.popitem()
+        if eng is not None:
+            self._engines.move_to_end(key)
+        else:
+            if len(self._engines) >= 4:  # bounded cache of device workspaces: drop the least recently used
+                _, old = self._engines.popitem(last=False)
                 old.close()
+            T, maxcap = Tcap, Lcap
             ctc_name = next(iter(self.part_scorers), None)
             eng = FusedStepEngine(
                 n_utts=B,
@@ -181,7 +190,10 @@ class BatchBeamSearch(torch.nn.Module):
         ctc_name = next(iter(self.part_scorers), None)
         if ctc_name is not None:
             ctc = self.part_scorers[ctc_name].ctc
-            logp = torch.zeros(B, T, V, dtype=torch.float32, device=device)
+            # frames past an utterance's length are never read (lgasr_set_posteriors applies the padding rule of
+            # ctc_prefix_score.py:46-49 itself), so the batch buffer is not cleared; one CTC-head call per utterance
+            # keeps every utterance's posteriors bit-identical to a single-utterance decode
+            logp = torch.empty(B, eng.T, V, dtype=torch.float32, device=device)
             for b, x in enumerate(xs):
                 logp[b, : lens[b]] = ctc.log_softmax(x.unsqueeze(0))[0].to(torch.float32)
             eng.set_posteriors(logp, lens)

@@ -59,9 +59,13 @@ struct lgasr_handle {
   StepLaunch sl2;    // k_step2 launch geometry
   size_t smem_step2;
   int cluster2;      // k_step2 launched as clusters of `beam` CTAs
+  int nth2;          // threads per CTA of k_step2 (256, 128 or 64)
   std::vector<void*> allocs;
   std::vector<long long> primer;
   std::vector<int> xlens;
+  int* h_xlen_pin;  // pinned staging of lgasr_set_posteriors: xlens[B]
+  cudaEvent_t ev_xlen;  // the copy out of h_xlen_pin has been performed
+  int* d_status;    // device status word: bit 0 = the ended-hypotheses pool of some utterance overflowed
   int* h_pin;  // pinned staging: n_run[B], done[B]
   int* h_begin_pin;  // pinned staging of lgasr_begin: maxlen[B], minlen[B], primer (int64)
   cudaEvent_t ev_begin;  // the copies out of h_begin_pin have been performed
@@ -108,6 +112,25 @@ static int dalloc(lgasr_handle* h, T** p, size_t n) {
     int rc_ = (x);        \
     if (rc_) return rc_;  \
   } while (0)
+
+// instances of k_step2 for a CTA size: [0..3] single CTAs (general, one matrix, two matrices, one matrix + trace),
+// [4..7] the same as thread-block clusters
+template <int NTH>
+static void step2_instances_of(const void** f) {
+  f[0] = (const void*)k_step2<NTH, false, 0, false>;
+  f[1] = (const void*)k_step2<NTH, false, 1, false>;
+  f[2] = (const void*)k_step2<NTH, false, 2, false>;
+  f[3] = (const void*)k_step2<NTH, false, 1, true>;
+  f[4] = (const void*)k_step2<NTH, true, 0, false>;
+  f[5] = (const void*)k_step2<NTH, true, 1, false>;
+  f[6] = (const void*)k_step2<NTH, true, 2, false>;
+  f[7] = (const void*)k_step2<NTH, true, 1, true>;
+}
+static void step2_instances(int nth, const void** f) {
+  if (nth == 256) step2_instances_of<256>(f);
+  else if (nth == 128) step2_instances_of<128>(f);
+  else step2_instances_of<64>(f);
+}
 
 extern "C" int lgasr_version(void) { return LGASR_VERSION; }
 extern "C" const char* lgasr_last_error(void) { return g_err; }
@@ -278,7 +301,11 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     rc |= dalloc(h, &d.n_run[p], d.B);
     rc |= dalloc(h, &d.done[p], d.B);
     rc |= dalloc(h, &d.rmeta[p], BW);
+    rc |= dalloc(h, &d.urec[p], d.B);
+    rc |= dalloc(h, &d.hrec[p], 2 * BW);
   }
+  rc |= dalloc(h, &d.ustat, d.B);
+  rc |= dalloc(h, &d.status, 1);
   rc |= dalloc(h, &d.arrive, d.B);
   rc |= dalloc(h, &d.step_flag, d.B);
   if (getenv("LGASR_TRACE")) {
@@ -307,18 +334,29 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
     lgasr_destroy(h);
     return LGASR_ENOMEM;
   }
-  if (cudaMallocHost(&h->h_pin, sizeof(int) * (2 * d.B + 2 * d.B * d.W)) != cudaSuccess) {
+  if (cudaMallocHost(&h->h_pin, sizeof(int) * (2 * d.B + 2 * d.B * d.W + 1)) != cudaSuccess ||
+      cudaMallocHost(&h->h_xlen_pin, sizeof(int) * d.B) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->ev_xlen, cudaEventDisableTiming) != cudaSuccess) {
     lgasr_destroy(h);
     return fail(LGASR_ENOMEM, "cudaMallocHost");
   }
   h->xlens.assign(d.B, d.T);
   h->cache_valid = false;
 
-  // opt in to large dynamic shared memory.  The attribute is per function and process wide, so it
-  // only ever grows (another handle may need more).
+  // opt in to large dynamic shared memory.  The attribute is per function AND per device, and another handle of the
+  // same device may need more: it only ever grows, with one high-water mark per device.
   {
     static std::mutex mu;
-    static size_t cur_rows[5] = {0, 0, 0, 0, 0}, cur_sel = 0;
+    constexpr int kMaxDev = 64;
+    static size_t hw_rows[kMaxDev][5] = {}, hw_sel[kMaxDev] = {}, hw_step[kMaxDev] = {};
+    static bool hw_np[kMaxDev] = {};
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    dev_id = dev_id < 0 || dev_id >= kMaxDev ? 0 : dev_id;
+    size_t* cur_rows = hw_rows[dev_id];
+    size_t& cur_sel = hw_sel[dev_id];
+    size_t& cur_step = hw_step[dev_id];
+    bool& np_set = hw_np[dev_id];
     std::lock_guard<std::mutex> lk(mu);
     cudaError_t e = cudaSuccess;
     if (h->smem_rows > cur_rows[h->NL]) {
@@ -329,7 +367,6 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       }
       if (e == cudaSuccess) cur_rows[h->NL] = h->smem_rows;
     }
-    static size_t cur_step = 0;
     if (e == cudaSuccess && h->fused && h->smem_step > cur_step) {
       const int sm = (int)h->smem_step;
       e = cudaFuncSetAttribute(k_step<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
@@ -343,7 +380,6 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       if (e == cudaSuccess) cur_step = h->smem_step;
     }
     if (e == cudaSuccess && h->cluster) {
-      static bool np_set = false;
       if (!np_set) {
         e = cudaFuncSetAttribute(k_step<false, true, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_step<true, true, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
@@ -416,6 +452,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       if (rpg < 1) rpg = 1;
       if (rpg > n_sel) rpg = n_sel;
       sl.rows_per_group = rpg;
+      sl.kk_full = (n_sel + kStepWarps - 1) / kStepWarps;
       const char* ncl = getenv("LGASR_NO_CLUSTER");
       h->cluster2 = d.W >= 2 && d.W <= 16 && !(ncl && ncl[0] == '1');
       const size_t base = sizeof(Step2Smem) + (size_t)6 * (d.Tp + 4) * sizeof(float) + (size_t)arena * sizeof(float);
@@ -426,17 +463,33 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       }
       // the attributes are per device: set them for every handle (cheap) instead of tracking high-water marks
       cudaError_t e = cudaSuccess;
-      const void* fns[6] = {(const void*)k_step2<false, 0>, (const void*)k_step2<false, 1>, (const void*)k_step2<false, 2>,
-                            (const void*)k_step2<true, 0>,  (const void*)k_step2<true, 1>,  (const void*)k_step2<true, 2>};
-      for (int i = 0; i < 6 && e == cudaSuccess; ++i)
-        e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step2);
+      // threads per CTA: the glue is paid per warp, so large grids (several waves) take fewer, fatter warps
+      {
+        const char* nt = getenv("LGASR_NTH");
+        h->nth2 = 128;
+        if (nt && (atoi(nt) == 64 || atoi(nt) == 128 || atoi(nt) == 256)) h->nth2 = atoi(nt);
+      }
+      const void* fns[8];
+      step2_instances(h->nth2, fns);
+      static size_t hw2[64][3] = {};
+      int dev_id = 0;
+      cudaGetDevice(&dev_id);
+      dev_id = dev_id < 0 || dev_id >= 64 ? 0 : dev_id;
+      size_t& cur2 = hw2[dev_id][h->nth2 == 256 ? 0 : h->nth2 == 128 ? 1 : 2];
+      // (the cluster instances get the attribute with the selection buffer included; a later fall-back to single CTAs
+      // launches with less, which is fine)
+      if (h->smem_step2 > cur2) {
+        for (int i = 0; i < 8 && e == cudaSuccess; ++i)
+          e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step2);
+        if (e == cudaSuccess) cur2 = h->smem_step2;
+      }
       if (e == cudaSuccess && h->cluster2) {
-        for (int i = 3; i < 6 && e == cudaSuccess; ++i)
+        for (int i = 4; i < 8 && e == cudaSuccess; ++i)
           e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         int ncl_max = 0;
         cudaLaunchConfig_t qc = {};
         qc.gridDim = dim3(d.W, d.B);
-        qc.blockDim = dim3(kStepThreads);
+        qc.blockDim = dim3(h->nth2);
         qc.dynamicSmemBytes = h->smem_step2;
         cudaLaunchAttribute qa[1];
         qa[0].id = cudaLaunchAttributeClusterDimension;
@@ -446,7 +499,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
         qc.attrs = qa;
         qc.numAttrs = 1;
         // clusters only pay while every utterance's cluster is resident at once (one wave)
-        if (e != cudaSuccess || cudaOccupancyMaxActiveClusters(&ncl_max, k_step2<true, 1>, &qc) != cudaSuccess || ncl_max < d.B) {
+        if (e != cudaSuccess || cudaOccupancyMaxActiveClusters(&ncl_max, fns[5], &qc) != cudaSuccess || ncl_max < d.B) {
           cudaGetLastError();
           e = cudaSuccess;
           h->cluster2 = 0;
@@ -474,6 +527,8 @@ extern "C" int lgasr_destroy(lgasr_handle* h) {
     cudaEventDestroy(h->rg_ev[1]);
   }
   if (h->h_pin) cudaFreeHost(h->h_pin);
+  if (h->h_xlen_pin) cudaFreeHost(h->h_xlen_pin);
+  if (h->ev_xlen) cudaEventDestroy(h->ev_xlen);
   if (h->h_begin_pin) cudaFreeHost(h->h_begin_pin);
   if (h->ev_begin) cudaEventDestroy(h->ev_begin);
   if (h->d_logp_stage) cudaFree(h->d_logp_stage);
@@ -497,15 +552,17 @@ extern "C" int lgasr_set_posteriors(lgasr_handle* h, const float* d_logp, const 
     if (l < 1 || l > d.T) return fail(LGASR_EINVAL, "xlens[%d]=%d outside [1,%d]", b, l, d.T);
     h->xlens[b] = l;
   }
-  CK(cudaMemcpyAsync(const_cast<int*>(d.xlen), h->xlens.data(), sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
+  // the lengths are staged in pinned memory owned by the handle: the call returns without synchronising the stream
+  CK(cudaEventSynchronize(h->ev_xlen));  // the previous call's copy has left the staging buffer
+  memcpy(h->h_xlen_pin, h->xlens.data(), sizeof(int) * d.B);
+  CK(cudaMemcpyAsync(const_cast<int*>(d.xlen), h->h_xlen_pin, sizeof(int) * d.B, cudaMemcpyHostToDevice, st));
+  CK(cudaEventRecord(h->ev_xlen, st));
   if (d.use_ctc) {
     if (!d_logp) return fail(LGASR_EINVAL, "null posteriors");
     dim3 grid((d.V + 63) / 64, (d.Tp + 63) / 64, d.B), block(32, 8);
     k_transpose_pad<<<grid, block, 0, st>>>(d_logp, const_cast<float*>(d.xT), d.xlen, d.T, d.Tp, d.V, d.blank, 0);
     LAUNCH_CK();
   }
-  // the host vector is read asynchronously by the copy above: make it safe to modify later
-  CK(cudaStreamSynchronize(st));
   h->have_post = 1;
   h->begun = 0;
   return LGASR_OK;
@@ -567,6 +624,7 @@ extern "C" int lgasr_begin(lgasr_handle* h, const int32_t* h_maxlen, const int32
     k_ctc_init_state<<<d.B, 128, d.Tp * sizeof(float), st>>>(d.xT, d.r[0], d.T, d.Tp, d.V, d.W, d.blank, d.W);
     LAUNCH_CK();
   }
+  CK(cudaMemsetAsync(d.status, 0, sizeof(int), st));
   k_begin<<<d.B, 128, 0, st>>>(d, h->d_primer, h->cfg.primer_len);
   LAUNCH_CK();
   h->pp = 0;
@@ -650,12 +708,13 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     cfg.numAttrs = na;
     // without the cluster the selection scratch aliases the arena: the extra buffer is not needed
     cfg.dynamicSmemBytes = h->smem_step2;
-    auto kern = k_step2<false, 0>;
-    if (use_cluster)
-      kern = sl.row_path == 1 ? k_step2<true, 1> : sl.row_path == 2 ? k_step2<true, 2> : k_step2<true, 0>;
-    else
-      kern = sl.row_path == 1 ? k_step2<false, 1> : sl.row_path == 2 ? k_step2<false, 2> : k_step2<false, 0>;
-    CK(cudaLaunchKernelEx(&cfg, kern, d, tm, sl, h->pp, h->rp, h->step));
+    const bool trc = d.trace != nullptr && sl.row_path == 1;  // the stamped instance exists for the one-matrix path
+    const void* fns[8];
+    step2_instances(h->nth2, fns);
+    const void* kern = fns[(use_cluster ? 4 : 0) + (trc ? 3 : sl.row_path)];
+    cfg.blockDim = dim3(h->nth2);
+    void* args[5] = {(void*)&d, (void*)&tm, (void*)&sl, (void*)&h->pp, (void*)&h->rp};
+    CK(cudaLaunchKernelExC(&cfg, kern, args));
     LAUNCH_CK();
     if (h->profiling) {
       CK(cudaEventRecord(pe[1], st));
@@ -815,7 +874,9 @@ extern "C" int lgasr_poll(lgasr_handle* h, int32_t* h_n_running, int32_t* h_done
   CK(cudaMemcpyAsync(pin + d.B, d.done[h->pp], sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
   if (h_parent) CK(cudaMemcpyAsync(pin + 2 * d.B, d.step_parent, sizeof(int) * BW, cudaMemcpyDeviceToHost, st));
   if (h_token) CK(cudaMemcpyAsync(pin + 2 * d.B + BW, d.step_tok, sizeof(int) * BW, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(pin + 2 * d.B + 2 * BW, d.status, sizeof(int), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  if (pin[2 * d.B + 2 * BW] & 1) return fail(LGASR_ESTATE, "ended-hypotheses pool overflow (Ecap = beam * max_len_cap = %d)", d.Ecap);
   int act = 0;
   for (int b = 0; b < d.B; ++b) {
     if (h_n_running) h_n_running[b] = pin[b];
@@ -831,8 +892,11 @@ extern "C" int lgasr_poll(lgasr_handle* h, int32_t* h_n_running, int32_t* h_done
 static int refresh_cache(lgasr_handle* h, cudaStream_t st) {
   Dev& d = h->d;
   h->c_n_ended.resize(d.B);
+  int status = 0;
   CK(cudaMemcpyAsync(h->c_n_ended.data(), d.n_ended, sizeof(int) * d.B, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&status, d.status, sizeof(int), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  if (status & 1) return fail(LGASR_ESTATE, "ended-hypotheses pool overflow (Ecap = beam * max_len_cap = %d)", d.Ecap);
   int mx = 0;
   for (int b = 0; b < d.B; ++b) mx = h->c_n_ended[b] > mx ? h->c_n_ended[b] : mx;
   const int NS = d.NS > 0 ? d.NS : 1;
@@ -1123,9 +1187,12 @@ extern "C" int lgasr_ctc_prefix_score(const float* d_xT, int T, int Tp, int V, i
   if (smem > 200 * 1024) return fail(LGASR_EINVAL, "T too large");
   {
     static std::mutex mu;
-    static size_t cur = 48 * 1024;
+    static size_t hw[64] = {};  // per device (the attribute is per function and device)
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    size_t& cur = hw[dev_id < 0 || dev_id >= 64 ? 0 : dev_id];
     std::lock_guard<std::mutex> lk(mu);
-    if (smem > cur) {
+    if (smem > 48 * 1024 && smem > cur) {
       cudaError_t e = cudaFuncSetAttribute(k_ctc_prefix_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
       cur = smem;
@@ -1146,9 +1213,12 @@ extern "C" int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blan
   if (smem > 200 * 1024) return fail(LGASR_EINVAL, "T too large");
   {
     static std::mutex mu;
-    static size_t cur = 48 * 1024;
+    static size_t hw[64] = {};  // per device (the attribute is per function and device)
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    size_t& cur = hw[dev_id < 0 || dev_id >= 64 ? 0 : dev_id];
     std::lock_guard<std::mutex> lk(mu);
-    if (smem > cur) {
+    if (smem > 48 * 1024 && smem > cur) {
       cudaError_t e = cudaFuncSetAttribute(k_ctc_select_state, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
       cur = smem;

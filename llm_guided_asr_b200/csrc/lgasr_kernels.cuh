@@ -66,6 +66,12 @@ struct Dev {
   float* best_by_len;    // [B][Lcap + 2]
   float* best_all;       // [B]
   long long* trace;      // debug: [B][W][2][16] clock64 stamps of k_step phases (NULL = off)
+  // packed copies of the state k_step2 reads at the top of a position (one 16-byte load each instead of a dozen
+  // scattered 4-byte loads): written next to the arrays above by k_begin / utt_select / utt_carry_done
+  int4* urec[2];         // [B]      (done, n_run, cur_len, 0)
+  int4* hrec[2];         // [B][W][2] (parent slot, last token, parent's last token, run_slot), (s_prev, score, 0, 0) as bits
+  int4* ustat;           // [B]      (xlen, maxlen, minlen, 0), fixed for the utterance
+  int* status;           // device status word: bit 0 = an eligible ended hypothesis did not fit the ended pool
 };
 
 // modes
@@ -621,6 +627,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
           d.end_meta[(long long)b * d.Ecap + my_end] = make_int4(step, j, new_len, last ? 1 : 0);
         } else {
           dest[j] = INT_MIN;
+          if (elig) atomicOr(d.status, 1);  // pool overflow: reported by lgasr_poll / the gather calls, never silent
         }
       }
 #pragma unroll
@@ -652,6 +659,7 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
       d.n_run[pp ^ 1][b] = nrun_new;
       d.cur_len[pp ^ 1][b] = cur_len + 1;
       d.done[pp ^ 1][b] = fin ? 1 : 0;
+      d.urec[pp ^ 1][b] = make_int4(fin ? 1 : 0, nrun_new, cur_len + 1, 0);
       *sh_nsel = nsel;
     }
   }
@@ -679,6 +687,8 @@ __device__ __forceinline__ void utt_select(const Dev& d, const Terms& tm, int b,
       d.s_prev[pp ^ 1][nrow] = psi;
       d.run_slot[pp ^ 1][nrow] = j;
       d.rmeta[pp ^ 1][nrow] = make_int4(h, tok, p_last[h], 0);
+      d.hrec[pp ^ 1][2 * nrow] = make_int4(h, tok, p_last[h], j);
+      d.hrec[pp ^ 1][2 * nrow + 1] = make_int4(__float_as_int(psi), __float_as_int(total), 0, 0);
       d.step_parent[nrow] = h;
       d.step_tok[nrow] = tok;
       sc_out = d.scores[pp ^ 1] + (long long)nrow * NS;
@@ -714,6 +724,7 @@ __device__ __forceinline__ void utt_carry_done(const Dev& d, int b, int pp) {
   d.n_run[pp ^ 1][b] = 0;
   d.cur_len[pp ^ 1][b] = d.cur_len[pp][b];
   d.done[pp ^ 1][b] = 1;
+  d.urec[pp ^ 1][b] = make_int4(1, 0, d.cur_len[pp][b], 0);
 }
 
 // stand-alone selection launch (used after k_score_rows, i.e. for the full-vocabulary CTC mode)
@@ -811,6 +822,10 @@ __global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_
     d.step_flag[b] = 0;
     d.n_ended[b] = 0;
     d.best_all[b] = -INFINITY;
+    const int dn = (d.maxlen[b] <= 0) ? 1 : 0;
+    d.urec[0][b] = make_int4(dn, 1, primer_len, 0);
+    d.urec[1][b] = make_int4(dn, 1, primer_len, 0);
+    d.ustat[b] = make_int4(d.xlen[b], d.maxlen[b], d.minlen[b], 0);
   }
   for (int i = tid; i < d.Lcap + 2; i += blockDim.x) d.best_by_len[(long long)b * (d.Lcap + 2) + i] = -INFINITY;
   for (int i = tid; i < W; i += blockDim.x) {
@@ -825,6 +840,10 @@ __global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_
     const int last = (int)primer[primer_len - 1];
     d.rmeta[0][b * W + i] = make_int4(-1, last, -1, 0);
     d.rmeta[1][b * W + i] = make_int4(-1, last, -1, 0);
+    for (int p = 0; p < 2; ++p) {
+      d.hrec[p][2 * (b * W + i)] = make_int4(-1, last, -1, -1);
+      d.hrec[p][2 * (b * W + i) + 1] = make_int4(0, 0, 0, 0);  // s_prev = score = 0.0f
+    }
   }
   for (int i = tid; i < primer_len; i += blockDim.x) {
     d.yseq[0][(long long)(b * W) * d.Lcap + i] = primer[i];

@@ -104,7 +104,10 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         else:
             r_prev = torch.stack([s[0] for s in state]).contiguous()
             s_prev = torch.stack([s[1] for s in state]).to(torch.float32).contiguous()
-        last = torch.as_tensor([int(yi[-1]) for yi in y], dtype=torch.int32, device=dev)
+        if torch.is_tensor(y):  # (n, L) prefixes: the last tokens stay on the device (no per-hypothesis sync)
+            last = y[:, -1].to(device=dev, dtype=torch.int32).contiguous()
+        else:
+            last = torch.as_tensor([int(yi[-1]) for yi in y], dtype=torch.int32, device=dev)
         scores, log_psi = self._score(last, olen, r_prev, s_prev, ids)
         return scores.to(m["dtype"]), (r_prev, log_psi, last, olen, "lgasr")
 

@@ -16,7 +16,7 @@ from typing import Any, List, Tuple
 import numpy as np
 import torch
 
-from .scorer_interface import BatchScorerInterface
+from ..scorer_interface import BatchScorerInterface
 
 LOGZERO = -10000000000.0  # espnet/nets/ctc_prefix_score.py:32
 

@@ -12,7 +12,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from llm_guided_asr_b200.device_cache import log_softmax_rows  # noqa: E402
 from llm_guided_asr_b200.engine import FusedStepEngine  # noqa: E402
-from llm_guided_asr_b200 import synthetic as syn  # noqa: E402
+from llm_guided_asr_b200.testing import synthetic as syn  # noqa: E402
 
 DEV = torch.device("cuda:0")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

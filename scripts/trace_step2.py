@@ -32,6 +32,9 @@ names = ["rows_start", "topS_done", "ctc_in", "state_done", "cand_in", "records"
 t0 = tr[:, 0:1]
 rel = (tr[:, :8] - t0).astype(np.float64)
 sel = tr[:, 7] > tr[:, 6]
+for i, n in ((8, "rows_in_regs"), (9, "threshold"), (13, "own_pushes"), (14, "all_pushes")):
+    v = (tr[:, i] - tr[:, 0]).astype(np.float64)
+    print(f"  row phase: {n:12s} median={np.median(v):9.0f} p10={np.percentile(v, 10):9.0f} p90={np.percentile(v, 90):9.0f} cycles")
 for i, n in enumerate(names):
     v = rel[:, i] if i < 7 else rel[sel, i]
     print(f"{n:12s} n={len(v):5d} median={np.median(v):9.0f} p10={np.percentile(v, 10):9.0f} p90={np.percentile(v, 90):9.0f} max={v.max():9.0f} cycles")

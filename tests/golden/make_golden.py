@@ -9,7 +9,7 @@ For every case below the reference ``BatchBeamSearch`` (``espnet/nets/batch_beam
 wired as ``espnet2/bin/asr_inference.py:173-181,309-315,352-362,379`` wires it, decodes a
 synthetic utterance on the CPU in fp32 with the reference ``CTCPrefixScorer`` /
 ``CTCPrefixScoreTH`` and ``LengthBonus``; the neural full scorers are replaced by the
-table scorers of ``llm_guided_asr_b200.synthetic`` (bit-reproducible ``(n, V)`` matrices).
+table scorers of ``llm_guided_asr_b200.testing.synthetic`` (bit-reproducible ``(n, V)`` matrices).
 Recorded per case: inputs, n-best (tokens, score, per-scorer scores), the hypotheses kept
 after every ``search`` call, and every ``CTCPrefixScoreTH.__call__`` (inputs + outputs).
 """
@@ -33,7 +33,7 @@ from espnet.nets.ctc_prefix_score import CTCPrefixScoreTH  # noqa: E402
 from espnet.nets.scorers.ctc import CTCPrefixScorer  # noqa: E402
 from espnet.nets.scorers.length_bonus import LengthBonus  # noqa: E402
 
-from llm_guided_asr_b200 import synthetic as syn  # noqa: E402
+from llm_guided_asr_b200.testing import synthetic as syn  # noqa: E402
 
 assert syn.BatchScorerInterface.__module__.startswith("espnet."), "reference interfaces not picked up"
 

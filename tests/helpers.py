@@ -7,7 +7,7 @@ import os
 import numpy as np
 import torch
 
-from llm_guided_asr_b200 import synthetic as syn
+from llm_guided_asr_b200.testing import synthetic as syn
 from oracle.beam_search_oracle import BeamSearchOracle, torch_scorer_fn
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -16,8 +16,10 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GOLDEN_NAMES = sorted(
     os.path.basename(p)[:-4]
     for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz"))
-    if os.path.basename(p) not in ("streaming.npz", "score_filter.npz")
+    if os.path.basename(p) not in ("streaming.npz", "score_filter.npz") and not os.path.basename(p).startswith("nb_")
 )
+# non-batch goldens (make_golden_nonbatch.py): reference BeamSearch + NumPy CTCPrefixScore
+NONBATCH_NAMES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "nb_*.npz")))
 
 # fp32 score tolerance of BASELINE.json's north_star: 1e-4 absolute.
 SCORE_ATOL = 1e-4

@@ -10,7 +10,7 @@ import pytest
 import torch
 
 from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer, LengthBonus, _lib
-from llm_guided_asr_b200 import synthetic as syn
+from llm_guided_asr_b200.testing import synthetic as syn
 from llm_guided_asr_b200.beam_search import length_bounds
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 @pytest.mark.parametrize("name", GOLDEN_NAMES)
 def test_scorer_calls_match_reference(name):
     from llm_guided_asr_b200 import CTCPrefixScorer
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     g = Golden(name)
     c = g.spec

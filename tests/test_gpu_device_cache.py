@@ -53,7 +53,7 @@ def test_log_softmax_rows_strided_input_and_output():
 
 def _stepped_engine(B, W, V, seed=0):
     from llm_guided_asr_b200.engine import FusedStepEngine
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     T, L = 40, 6
     eos = V - 1
@@ -114,7 +114,7 @@ def _full_forward_fn(dec, memory):
 @pytest.mark.parametrize("fused_lsm", [True, False])
 def test_device_cached_decoder_decode(fused_lsm):
     from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer, LengthBonus
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
     from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer
 
     V, D, beam = 120, 32, 4
@@ -165,7 +165,7 @@ def test_device_cached_decoder_cuda_graphs_replay_across_batches():
     of the same shape (other encoder outputs, other lengths, a primer of three tokens); results must equal the
     eager device-cache path."""
     from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
     from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer
 
     V, beam = 96, 3
@@ -200,7 +200,7 @@ def test_device_cached_decoder_and_lm_together(graphs):
     """Decoder and language model both behind the device protocol (two cached scorers, two fused terms) against
     the same search with the reference's host-side state protocol; two batches, the second replays graphs."""
     from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
     from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer, DeviceCachedLMScorer
 
     V, beam = 80, 4
@@ -265,7 +265,7 @@ def test_fused_search_with_score_filter_and_primer():
     """OWSM-style decode: <sos><lang><task> primer, timestamp rules as an extra full scorer (weight 1.0) whose
     -inf entries go through the fusion, the pre-beam and the final top-k; against the oracle search."""
     from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
     from llm_guided_asr_b200.score_filter import ScoreFilter
     from oracle.score_filter_oracle import score_filter
 

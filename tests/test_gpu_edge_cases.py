@@ -34,7 +34,7 @@ def _check(nbest, ref, n_min=1):
 
 def _case(seed, T, V, beam, ntok, weights, with_lm, key="full", maxr=0.0):
     from llm_guided_asr_b200 import CTCPrefixScorer, LengthBonus
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     dev = torch.device("cuda:0")
     eos = V - 1
@@ -104,7 +104,7 @@ def test_all_equal_rows_overflow_rounds():
     """Every decoder score equal: the pre-beam set is decided purely by the index tie-break and the
     pending list (256 entries) overflows on every row -> the multi-round path."""
     from llm_guided_asr_b200 import CTCPrefixScorer
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     dev = torch.device("cuda:0")
     T, V, beam = 30, 1200, 4
@@ -136,7 +136,7 @@ def _replay_host_equals_stepping():
     """Whole-batch replay from host buffers (graph + PDL launches, double-buffered copies) must give
     exactly what position-by-position stepping gives: B = 8 utterances, ragged lengths, V = 5000."""
     from llm_guided_asr_b200.engine import FusedStepEngine
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     dev = torch.device("cuda:0")
     B, T, V, W, S, L = 8, 120, 5000, 10, 15, 12
@@ -197,7 +197,7 @@ def test_replay_instances_equal_stepping_on_every_staging_path(monkeypatch, V, n
     griddepcontrol.wait, four CTC warps) must reproduce position-by-position stepping (the side-by-side
     instance) bit for bit on every staging path; ragged lengths, an utterance that finishes early."""
     from llm_guided_asr_b200.engine import FusedStepEngine
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     monkeypatch.setenv("LGASR_FLAGS", flags)
     dev = torch.device("cuda:0")

@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 
 def build_search(g, device):
     from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer, LengthBonus
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     c = g.spec
     dec, lm, V = torch_scorers(g, device)
@@ -67,7 +67,7 @@ def test_decode_batch_equals_single_and_oracle():
     c = g.spec
     dev = torch.device("cuda:0")
     bs = build_search(g, dev)
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     xs = [torch.from_numpy(g["logp"]).to(dev)]
     # ragged batch: shorter utterances made from other seeds

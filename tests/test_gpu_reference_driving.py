@@ -1,0 +1,130 @@
+"""INTEGRATION.md level 1 ("scorer only"): the UNMODIFIED reference search objects drive this package's CUDA
+``CTCPrefixScorer`` through the plug-in API, and the non-batch scorer API is checked call by call.
+
+* every recorded ``CTCPrefixScore.__call__`` of the reference's NumPy scorer (``ctc_prefix_score.py:272-359``) is
+  replayed through ``CTCPrefixScorer.score_partial`` (no reference needed at test time);
+* with ``baseline/_ref`` present (``scripts/install_ref.sh``; it travels to the GPU box), the reference's own
+  ``BeamSearch`` (non-batch, ``beam_search.py:316-383``) and ``BatchBeamSearch`` (``batch_beam_search.py``) run on
+  ``cuda`` with this package's scorer in place of theirs and must reproduce the goldens recorded from the reference.
+
+Bar: tokens bit-exact, scores / log psi / states within 1e-4 abs (fp32; log-zero entries relative 1e-6).
+"""
+
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import GOLDEN_DIR, NONBATCH_NAMES, SCORE_ATOL, Golden
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+LOGZERO = -1.0e10
+
+
+def _have_ref():
+    try:
+        import espnet.nets.batch_beam_search  # noqa: F401
+
+        return True
+    except Exception:
+        return False
+
+
+def _ours_from_ref_state(r_prev, Tp):
+    """reference state (T, 2) = (r^n, r^b) -> this package's (2, Tp) = (r^n, log(r^n + r^b))."""
+    T = r_prev.shape[0]
+    out = np.full((2, Tp), LOGZERO, np.float32)
+    out[0, :T] = r_prev[:, 0]
+    out[1, :T] = np.logaddexp(r_prev[:, 0], r_prev[:, 1]).astype(np.float32)
+    return out
+
+
+@pytest.mark.parametrize("name", NONBATCH_NAMES)
+def test_score_partial_replays_reference_numpy_scorer_calls(name):
+    from llm_guided_asr_b200 import CTCPrefixScorer
+    from llm_guided_asr_b200.testing import synthetic as syn
+
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    spec = json.loads(str(z["spec"]))
+    x = torch.from_numpy(z["logp"]).to(DEV)
+    sc = CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=spec["eos"])
+    prev0, r0 = sc.init_state(x)
+    T, Tp = sc.impl["T"], sc.impl["Tp"]
+    assert float(prev0) == 0.0
+    for i in range(int(z["n_calls"])):
+        y, cs, r_prev = z[f"call{i}_y"], z[f"call{i}_cs"], z[f"call{i}_r_prev"]
+        state = (torch.zeros((), device=DEV), torch.from_numpy(_ours_from_ref_state(r_prev, Tp)).to(DEV))
+        tscore, (psi, r_new) = sc.score_partial(torch.from_numpy(y).to(DEV), torch.from_numpy(cs).to(DEV), state, x)
+        want = z[f"call{i}_log_psi"]
+        np.testing.assert_allclose(psi.cpu().numpy(), want, atol=SCORE_ATOL, rtol=1e-6)
+        np.testing.assert_allclose(tscore.cpu().numpy(), want, atol=SCORE_ATOL, rtol=1e-6)  # prev_score is 0 here
+        r_ref = z[f"call{i}_r"]  # (S, T, 2)
+        got = r_new.cpu().numpy()  # (S, 2, Tp)
+        special = (cs == spec["eos"]) | (cs == 0)
+        for j in range(len(cs)):
+            if special[j]:
+                continue  # the reference's eos / blank "states" are never selected (the hypothesis ends)
+            np.testing.assert_allclose(got[j, 0, :T], r_ref[j, :, 0], atol=SCORE_ATOL, rtol=1e-6)
+            np.testing.assert_allclose(got[j, 1, :T], np.logaddexp(r_ref[j, :, 0], r_ref[j, :, 1]), atol=SCORE_ATOL, rtol=1e-6)
+
+
+def _scorers(table, table_lm, V, eos):
+    from espnet.nets.scorers.length_bonus import LengthBonus
+
+    from llm_guided_asr_b200 import CTCPrefixScorer
+    from llm_guided_asr_b200.testing import synthetic as syn
+    from llm_guided_asr_b200.scorer_interface import USING_REFERENCE_INTERFACES
+
+    assert USING_REFERENCE_INTERFACES, "conftest.py puts baseline/_ref on the path before the package is imported"
+    return dict(decoder=syn.PrefixTableScorer(torch.from_numpy(table).to(DEV)),
+                ctc=CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=eos), length_bonus=LengthBonus(V),
+                lm=syn.PrefixTableScorer(torch.from_numpy(table_lm).to(DEV)))
+
+
+@pytest.mark.skipif(not _have_ref(), reason="baseline/_ref not installed (scripts/install_ref.sh)")
+@pytest.mark.parametrize("name", NONBATCH_NAMES)
+def test_reference_nonbatch_beam_search_drives_cuda_scorer(name):
+    from espnet.nets.beam_search import BeamSearch
+
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    c = json.loads(str(z["spec"]))
+    V, eos = c["V"], c["eos"]
+    weights = dict(decoder=1.0 - c["ctc"], ctc=c["ctc"], lm=c["lm"], length_bonus=c["pen"])
+    bs = BeamSearch(beam_size=c["beam"], weights=weights, scorers=_scorers(z["table"], z["table_lm"], V, eos), sos=eos, eos=eos,
+                    vocab_size=V, token_list=None, pre_beam_score_key=c["key"])
+    bs.to(device=DEV, dtype=torch.float32).eval()
+    with torch.no_grad():
+        nbest = bs(x=torch.from_numpy(z["logp"]).to(DEV), maxlenratio=c["maxr"], minlenratio=0.0)
+    assert len(nbest) == int(z["n_nbest"])
+    for i, h in enumerate(nbest):
+        ln = int(z["nbest_len"][i])
+        assert h.yseq.tolist() == z["nbest_yseq"][i, :ln].tolist()
+        assert abs(float(h.score) - float(z["nbest_score"][i])) <= SCORE_ATOL
+
+
+@pytest.mark.skipif(not _have_ref(), reason="baseline/_ref not installed (scripts/install_ref.sh)")
+@pytest.mark.parametrize("name", ["an4_shape", "lm_bonus", "peaky_lm", "peaky_minlen", "key_decoder", "primer", "mid_vocab",
+                                  "normalize_length", "beam1"])
+def test_reference_batch_beam_search_drives_cuda_scorer(name):
+    """The strongest drop-in proof: reference BatchBeamSearch + this package's CTCPrefixScorer."""
+    from espnet.nets.batch_beam_search import BatchBeamSearch
+    from espnet.nets.beam_search import BeamSearch
+
+    g = Golden(name)
+    c = g.spec
+    V, eos = c["V"], c["eos"]
+    bs = BeamSearch(beam_size=c["beam"], weights=g.weights, scorers=_scorers(g["table"], g["table_lm"], V, eos), sos=c["sos"],
+                    eos=eos, vocab_size=V, token_list=None, pre_beam_score_key=c["key"],
+                    normalize_length=c.get("norm", False), hyp_primer=c.get("primer"))
+    bs.__class__ = BatchBeamSearch  # espnet2/bin/asr_inference.py:379
+    bs.to(device=DEV, dtype=torch.float32).eval()
+    with torch.no_grad():
+        nbest = bs(x=torch.from_numpy(g["logp"]).to(DEV), maxlenratio=c["maxr"], minlenratio=c["minr"])
+    ref = g.nbest()
+    assert len(nbest) == len(ref) >= 1
+    for h, (toks, score) in zip(nbest, ref):
+        assert h.yseq.tolist() == toks
+        assert abs(float(h.score) - score) <= SCORE_ATOL

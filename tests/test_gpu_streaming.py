@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 
 def test_cuda_scorer_streaming_matches_reference():
     from llm_guided_asr_b200 import CTCPrefixScorer
-    from llm_guided_asr_b200 import synthetic as syn
+    from llm_guided_asr_b200.testing import synthetic as syn
 
     dev = torch.device("cuda:0")
     eos = int(G["eos"])

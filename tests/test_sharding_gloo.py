@@ -11,7 +11,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from llm_guided_asr_b200 import sharding
-from llm_guided_asr_b200 import synthetic as syn
+from llm_guided_asr_b200.testing import synthetic as syn
 from oracle.beam_search_oracle import BeamSearchOracle, torch_scorer_fn
 
 V, BEAM, EOS = 40, 3, 39
