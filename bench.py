@@ -15,9 +15,14 @@ matrices are out of the path.
   value : utts/s with posteriors and matrices already resident in HBM
   e2e   : utts/s through the C ABI from HOST (pinned) buffers, H2D of posteriors + every matrix and
           D2H of the n-best inside the timed region
-  roofline : k_step (the one kernel of a decode position) algorithmic bytes / CUDA-event duration vs
-          the measured HBM copy bandwidth of MEASURED_PEAKS.json
-  cpu_baseline / --impl reference : the oracle port of the reference algorithm on the host cores.
+  roofline : the step kernel's algorithmic bytes / CUDA-event duration vs the measured HBM copy bandwidth of
+          MEASURED_PEAKS.json, for the STEPPING launches (what a scorer in the loop issues; primary), the graph
+          replay, and (roofline_b512) with configs[4]'s per-GPU batch of 512 utterances in flight; `traffic` is
+          read from the committed ncu capture (profiles/r02_kstep_traffic.json)
+  cpu_baseline / --impl reference : the UNMODIFIED reference (baseline/_ref, scripts/install_ref.sh) on all host
+          cores, one single-threaded process per utterance; reference_gpu / --impl reference_gpu: the same classes
+          on cuda:0 (the reference's own GPU PyTorch path), one utterance at a time
+  parity : the whole n-best list of all 64 utterances against the reference's output (tokens, scores).
 
 Multi-GPU: every rank decodes its own 64 utterances (weak scaling, no data-path collective), then a
 final gather of the best hypotheses to rank 0.
@@ -39,8 +44,6 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 CFG = dict(B=64, T=374, V=5000, beam=10, S=15, ctc_weight=0.3, L=64, K=1)
-# dram__bytes_read.sum + dram__bytes_write.sum of one steady-state k_step launch (ncu --set full, profiles/)
-TRAFFIC_BYTES_PER_LAUNCH = 34591744  # profiles/r01h: 30.24 MB read + 4.35 MB written (k_step<0,0,1>)
 AUDIO_SEC = 15.0
 
 
@@ -87,17 +90,18 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         while not self.stop:
             try:
-                out = subprocess.run(
-                    ["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                    capture_output=True, text=True, timeout=5,
-                ).stdout.strip().split(",")
-                self.samples.append((float(out[0]), float(out[1])))
-                for n, v in zip(names, out[2:]):
-                    if v.strip().lower().startswith("active"):
-                        self.reasons.add(n)
+                cmd = ["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits"]
+                if self.index is not None:  # None: every GPU of the box in one call (one sampler per node)
+                    cmd += ["-i", str(self.index)]
+                for ln in subprocess.run(cmd, capture_output=True, text=True, timeout=5).stdout.strip().splitlines():
+                    out = ln.split(",")
+                    self.samples.append((float(out[0]), float(out[1])))
+                    for n, v in zip(names, out[2:]):
+                        if v.strip().lower().startswith("active"):
+                            self.reasons.add(n)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.1)
 
     def __enter__(self):
         self.th.start()
@@ -280,6 +284,77 @@ def bench_config(cfg):
     }
 
 
+def traffic_record():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one steady-state launch of the step kernel, from the committed
+    ncu --set full capture (profiles/r02_kstep_traffic.json, written by scripts/ncu_traffic.py from the .ncu-rep)."""
+    p = os.path.join(ROOT, "profiles", "r02_kstep_traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    r = json.load(open(p))
+    return int(r["dram_bytes_per_launch"]), r
+
+
+def launch_time_us(eng, mats, consts, wts, V, mode, reps, first=1):
+    """Mean duration of one step-kernel launch (us), CUDA events on the launching stream.
+    mode "step": lgasr_step launches queued back to back (what a scorer in the loop issues; no poll between them),
+    positions first..L-1 timed (position 0 runs one hypothesis per utterance); "replay": the graph + programmatic
+    dependent launch replay of all L positions."""
+    B = eng.B
+    L = len(mats)
+    out = []
+    for _ in range(reps + 1):
+        eng.begin([L] * B, [0] * B, [V - 1])
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if mode == "step":
+            for i in range(first):
+                eng.step(mats[i], consts, wts)
+            e0.record()
+            for i in range(first, L):
+                eng.step(mats[i], consts, wts)
+            e1.record()
+            n = L - first
+        else:
+            e0.record()
+            eng.replay(mats, consts, wts, ld=V)
+            e1.record()
+            n = L
+        torch.cuda.synchronize()
+        out.append(e0.elapsed_time(e1) * 1e3 / n)
+    return statistics.mean(out[1:]), n * reps
+
+
+def roofline_b512(dev, cfg, peak, reps=3):
+    """The same kernel with configs[4]'s per-GPU batch in flight (512 utterances, device-generated inputs, 16 positions):
+    several waves of CTAs, ticket exchange."""
+    from llm_guided_asr_b200.engine import FusedStepEngine
+
+    B, T, V, W, L = 512, cfg["T"], cfg["V"], cfg["beam"], 16
+    g = torch.Generator(device=dev).manual_seed(7)
+    logp = torch.log_softmax(3.0 * torch.randn(B, T, V, device=dev, generator=g), dim=-1)
+    tables = torch.log_softmax(2.0 * torch.randn(L, B * W, V, device=dev, generator=g), dim=-1)
+    eng = FusedStepEngine(B, T, V, W, cfg["S"], ["decoder"], "full", True, cfg["ctc_weight"], V - 1, V - 1, L, 1, False, device=dev)
+    eng.set_posteriors(logp, [T] * B)
+    mats = [[tables[i]] for i in range(L)]
+    wts = [1.0 - cfg["ctc_weight"]]
+    us_step, n1 = launch_time_us(eng, mats, [0.0], wts, V, "step", reps)
+    us_rep, _ = launch_time_us(eng, mats, [0.0], wts, V, "replay", reps)
+    ab = B * (4 * (T * (W * cfg["S"] + 1 + 4 * W) + cfg["K"] * W * V) + 16 * W)  # T_eff ~ T for the first positions
+    nrun = [[1] * B] + [[W] * B] * (L - 1)
+    ab_step = algorithmic_bytes(dict(cfg, B=B), nrun[1:]) / (L - 1)
+    ab_rep = algorithmic_bytes(dict(cfg, B=B), nrun) / L
+    info = eng.launch_info()
+    eng.close()
+    del logp, tables
+    torch.cuda.empty_cache()
+    return {
+        "bound": "hbm", "kernel": "k_step (stepping launches)", "utterances_in_flight": B,
+        "achieved": ab_step / us_step / 1e3, "peak": peak, "unit": "GB/s", "frac": ab_step / us_step / 1e3 / peak,
+        "avg_launch_us": us_step, "algorithmic_bytes_per_launch": ab_step,
+        "replay": {"avg_launch_us": us_rep, "achieved": ab_rep / us_rep / 1e3, "frac": ab_rep / us_rep / 1e3 / peak},
+        "launches_timed": n1, "k_step": info,
+    }
+
+
 def run_ours(args, rank, world, local_rank):
     from llm_guided_asr_b200 import _lib
     from llm_guided_asr_b200.engine import FusedStepEngine
@@ -314,27 +389,30 @@ def run_ours(args, rank, world, local_rank):
         eng.replay_host(h_logp, xl, mx, mn, [eos], mats_host, consts, wts, ld=V)
         return eng.gather_best()  # best hypothesis of every utterance: one D2H + one C call
 
+    # one clock sampler per node (rank 0 watches every GPU of the box), not one per rank
+    sampler = ClockSampler(None if world > 1 else local_rank) if rank == 0 else None
+
     # ---- value: resident inputs -------------------------------------------------------------
     for _ in range(args.warmup):
         decode_resident()
     barrier()
     n0 = _lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clk:
-        ev0.record()
-        for _ in range(args.steps):
-            decode_resident()
-        ev1.record()
-        barrier()
+    if sampler:
+        sampler.__enter__()
+    ev0.record()
+    for _ in range(args.steps):
+        decode_resident()
+    ev1.record()
+    barrier()
     launches = _lib.launch_count() - n0
     ms_total = ev0.elapsed_time(ev1)
     results_resident = eng.gather_best()
+    nbest_resident = [eng.gather_ended(b) for b in range(B)] if rank == 0 else None
 
-    # ---- roofline pass 1: position by position (the n_run history for the algorithmic bytes, and the
-    #      launch duration seen by a caller that steps: CUDA events around every launch) ---------------
+    # ---- roofline: the launches a scorer in the loop issues (stepping instance, primary) and the replay ---------
     eng.set_posteriors(d_logp, xl)
     eng.begin(mx, mn, [eos])
-    eng.set_profiling(True)
     n_run_hist = []
     nrun = np.ones(B, dtype=np.int64)
     for i in range(L):
@@ -344,28 +422,21 @@ def run_ours(args, rank, world, local_rank):
         nrun = np.where(np.asarray(done) != 0, 0, nrun)
         if act == 0:
             break
-    ms_rows, ms_sel, nsteps = eng.get_profile()
-    eng.set_profiling(False)
-    abytes = algorithmic_bytes(cfg, n_run_hist)
+    step_results = eng.gather_best()
+    assert step_results == results_resident, "stepping and replay decodes disagree"
     peak, peak_kind = peaks()
-    # ---- roofline pass 2: the same launches back to back (the replay of the timed region), CUDA events on
-    #      the launching stream around the L launches only (no transpose, no init) -----------------------
-    rep_ms = []
-    for _ in range(max(3, args.steps)):
-        eng.begin(mx, mn, [eos])
-        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        r0.record()
-        eng.replay(mats_dev, consts, wts, ld=V)
-        r1.record()
-        torch.cuda.synchronize(dev)
-        rep_ms.append(r0.elapsed_time(r1))
-    launch_ms = statistics.mean(rep_ms[1:]) / len(n_run_hist)
-    achieved = abytes / len(n_run_hist) / (launch_ms * 1e-3) / 1e9
+    reps = max(3, min(args.steps, 10))
+    us_step, n_timed = launch_time_us(eng, mats_dev, consts, wts, V, "step", reps)
+    us_rep, _ = launch_time_us(eng, mats_dev, consts, wts, V, "replay", reps)
+    ab_step = algorithmic_bytes(cfg, n_run_hist[1:]) / (len(n_run_hist) - 1)
+    ab_rep = algorithmic_bytes(cfg, n_run_hist) / len(n_run_hist)
+    traffic, traffic_rec = traffic_record()
 
     # ---- e2e: host buffers ---------------------------------------------------------------------
     for _ in range(max(1, min(args.warmup, 2))):
         decode_host()
     barrier()
+
     def gather_results(res):
         # the final hypothesis gather (tiny): padded int32 tokens + fp32 score bits, one NCCL gather to rank 0
         Lm = L + 2
@@ -383,18 +454,17 @@ def run_ours(args, rank, world, local_rank):
         gather_results(results_resident)  # communicator set-up outside the timed region
         barrier()
     gather_s = 0.0
-    with ClockSampler(local_rank) as clk2:  # the e2e leg is a timed region too
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            res_host = decode_host()
-            if world > 1:
-                tg = time.perf_counter()
-                gather_results(res_host)
-                gather_s += time.perf_counter() - tg
-        torch.cuda.synchronize(dev)
-        e2e_s = time.perf_counter() - t0
-    clk.samples += clk2.samples
-    clk.reasons |= clk2.reasons
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res_host = decode_host()
+        if world > 1:
+            tg = time.perf_counter()
+            gather_results(res_host)
+            gather_s += time.perf_counter() - tg
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    if sampler:
+        sampler.__exit__()
     assert res_host == results_resident, "host-buffer and resident decodes disagree"
 
     t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device=dev)
@@ -407,20 +477,43 @@ def run_ours(args, rank, world, local_rank):
     if rank != 0:
         return
 
-    # ---- cpu baseline + parity on a bounded sample (rank 0) ------------------------------------
-    cpu = None
-    parity = None
+    # ---- rank 0, one GPU: the reference itself beside it (CPU on all host cores, GPU PyTorch) + parity ----------
+    cpu = parity = ref_gpu = b512 = None
     if args.gpus == 1 and not args.no_cpu:
+        b512 = roofline_b512(dev, cfg, peak)
         cores = os.cpu_count() or 1
-        n_s = min(B, cores)
-        dt, ores = cpu_oracle_run(logp, tables, cfg, list(range(n_s)), cores)
-        cpu = {
-            "value": n_s / dt, "unit": "utts/s", "cores": cores, "kind": "port",
-            "sample": f"{n_s} of the {B} utterances x {L} positions, one process per core (numpy oracle port)",
-        }
-        tok_equal = all(results_resident[b][0] == ores[b][0][0] for b in range(n_s))
-        maxdiff = max(abs(results_resident[b][1] - ores[b][0][1]) for b in range(n_s))
-        parity = {"utts_checked": n_s, "tokens_equal": bool(tok_equal), "max_abs_score_diff": maxdiff}
+        # the whole batch through the reference on the host cores (about 64 / cores x 2 s)
+        dt, rres, kind = reference_cpu_run(logp, tables, cfg, list(range(B)), L, cores)
+        what = ("unmodified reference (baseline/_ref: BatchBeamSearch + CTCPrefixScoreTH, torch CPU fp32)" if kind == "reference"
+                else "numpy oracle port (baseline/_ref not installed)")
+        cpu = {"value": B / dt, "unit": "utts/s", "cores": cores, "kind": kind,
+               "sample": f"all {B} utterances x {L} positions, one single-threaded process per core: {what}"}
+        # parity of the whole n-best list of every utterance against the reference's output
+        tok_equal, maxdiff, n_hyps = True, 0.0, 0
+        for b in range(B):
+            toks, score, _ = nbest_resident[b]
+            order = sorted(range(len(toks)), key=lambda e: -float(score[e]))
+            ref = rres[b]
+            tok_equal = tok_equal and len(order) == len(ref)
+            for e, (rt, rs) in zip(order, ref):
+                tok_equal = tok_equal and (toks[e] == rt)
+                maxdiff = max(maxdiff, abs(float(score[e]) - rs))
+                n_hyps += 1
+        parity = {"against": kind, "utts_checked": B, "hypotheses_checked": n_hyps, "tokens_equal": bool(tok_equal),
+                  "max_abs_score_diff": maxdiff, "tolerance": 1e-4}
+        # the reference's own GPU PyTorch path (north_star's 20x denominator), in a process of its own
+        try:
+            out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference_gpu", "--steps", "5"],
+                                 capture_output=True, text=True, timeout=600).stdout.strip().splitlines()
+            rg = json.loads(out[-1]) if out else {"unavailable": "no output"}
+            if "best" in rg:
+                best = rg.pop("best")
+                rg["tokens_equal_ours"] = all(results_resident[i][0] == best[i][0] for i in range(len(best)))
+                rg["max_abs_score_diff_ours"] = max(abs(results_resident[i][1] - best[i][1]) for i in range(len(best)))
+                rg["ours_over_reference_gpu"] = value / rg["value"]
+            ref_gpu = rg
+        except Exception as e:  # the leg is informative: never fail the bench line on it
+            ref_gpu = {"unavailable": repr(e)[:200]}
 
     line = {
         "metric": "decode_utts_per_sec",
@@ -449,17 +542,21 @@ def run_ours(args, rank, world, local_rank):
         },
         "gpu_launches": int(launches),
         "roofline": {
-            "bound": "hbm", "kernel": "k_step", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak, "peak_kind": peak_kind, "traffic": TRAFFIC_BYTES_PER_LAUNCH,
-            "algorithmic_bytes_per_launch": abytes / max(nsteps, 1),
-            "avg_launch_us": launch_ms * 1e3,
-            "how": "CUDA events on the launching stream around the 64 back-to-back k_step launches of one decode (graph replay, launch gaps included), mean of the timed decodes / 64",
-            "stepping_launch_us": (ms_rows + ms_sel) * 1e3 / max(nsteps, 1),
-            "launches_timed": len(n_run_hist) * (len(rep_ms) - 1),
+            "bound": "hbm", "kernel": "k_step (stepping launches: the instance a scorer in the loop uses)",
+            "achieved": ab_step / us_step / 1e3, "peak": peak, "unit": "GB/s", "frac": ab_step / us_step / 1e3 / peak,
+            "peak_kind": peak_kind, "traffic": traffic, "traffic_source": traffic_rec,
+            "algorithmic_bytes_per_launch": ab_step, "avg_launch_us": us_step,
+            "how": "CUDA events on the launching stream around lgasr_step launches queued back to back (positions 1..63 of a decode, no host sync between them), mean over the timed decodes",
+            "launches_timed": n_timed,
+            "replay": {"kernel": "k_step (graph + programmatic dependent launch replay)", "avg_launch_us": us_rep,
+                       "achieved": ab_rep / us_rep / 1e3, "frac": ab_rep / us_rep / 1e3 / peak,
+                       "algorithmic_bytes_per_launch": ab_rep},
         },
+        "roofline_b512": b512,
         "cpu_baseline": cpu,
+        "reference_gpu": ref_gpu,
         "parity": parity,
-        "clocks": clk.summary(),
+        "clocks": sampler.summary() if sampler else None,
     }
     print(json.dumps(line), flush=True)
 
