@@ -216,6 +216,22 @@ int lgasr_reorder_rows(lgasr_handle* h, void* d_dst, const void* d_src, int64_t 
 int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t ld_in, float* d_out, int64_t ld_out, int rows,
                            int vocab, void* stream);
 
+/* Normaliser only: d_lse[r] = logsumexp(d_logits[r][0:vocab)) in fp32 (same kernel, no (n, V) output).  Together with
+ * lgasr_step_ex this is the LLM logits hand-off: the 32 k - 128 k wide row of
+ * LLMGuidedTransformerDecoder.batch_score (espnet2/asr/decoder/transformer_decoder.py:1115-1132; bf16 logits,
+ * espnet2/asr/llm/llama.py:27,47-52) is read ONCE by the step, at 2 bytes per entry, instead of
+ * bf16 read + fp32 write (log_softmax) + fp32 read (step) = 10 bytes per entry. */
+int lgasr_row_logsumexp(const void* d_logits, int dtype, int64_t ld_in, float* d_lse, int rows, int vocab, void* stream);
+
+/* lgasr_step with typed term matrices: h_term_dtype[k] is LGASR_F32 or LGASR_BF16 (storage of matrix k);
+ * h_term_norm[k] (may be NULL, and the array itself may be NULL) is a device array of B*beam fp32 normalisers:
+ * the score of entry v of row r is float(matrix[r][v]) - norm[r], i.e. log_softmax(logits) when norm = logsumexp.
+ * The fp32 fusion order is that of lgasr_step.  Rows must be 16-byte aligned (ld % 4 == 0 for fp32, % 8 for bf16 is
+ * not required: 8-byte loads) and vocab % 4 == 0.  The pre-beam key term, if any, must be plain fp32. */
+int lgasr_step_ex(lgasr_handle* h, const void* const* h_term_ptr, const int32_t* h_term_dtype,
+                  const float* const* h_term_norm, const float* h_term_const, const float* h_term_weight, int64_t ld,
+                  void* stream);
+
 /* Timestamp-rule full scorer of the OWSM recipe = ScoreFilter.batch_score
  * (espnet2/bin/s2t_inference.py:47-146): d_out[r][0:vocab) = 0.0 or -inf from the prefix
  * d_yseq[r][0:cur_len) (int64, leading dimension ld_y; e.g. the handle's yseq view).  Where the reference

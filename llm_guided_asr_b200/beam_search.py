@@ -217,7 +217,7 @@ class BatchBeamSearch(torch.nn.Module):
         for i in range(max(maxlen)):
             cur_len = len(primer) + i
             yseq = eng.view(0)  # (B, W, Lcap) current running prefixes
-            mats, consts = [], []
+            mats, consts, norm_at = [], [], {}
             new_states = {k: [None] * B for k in names}
             for k in names:
                 d = self.full_scorers[k]
@@ -226,7 +226,12 @@ class BatchBeamSearch(torch.nn.Module):
                     consts.append(float(d.constant_score))
                     continue
                 if hasattr(d, "batch_score_padded"):  # scorer that fills the padded row layout itself
-                    mats.append(d.batch_score_padded(yseq[:, :, :cur_len], n_run, done))
+                    res = d.batch_score_padded(yseq[:, :, :cur_len], n_run, done)
+                    if isinstance(res, tuple):  # (logits, per-row logsumexp): normalised inside the step kernel
+                        mats.append(res[0])
+                        norm_at[len(mats) - 1] = res[1]
+                    else:
+                        mats.append(res)
                     consts.append(0.0)
                     continue
                 if B == 1 and not done[0]:
@@ -263,7 +268,7 @@ class BatchBeamSearch(torch.nn.Module):
                 else:
                     mats.append(pad[k])
                     consts.append(0.0)
-            eng.step(mats, consts, wts)
+            eng.step(mats, consts, wts, [norm_at.get(j) for j in range(len(mats))] if norm_at else None)
             steps += 1
             for k in names:  # device-resident caches: parent-indexed gather queued behind the step
                 if hasattr(self.full_scorers[k], "device_reorder"):

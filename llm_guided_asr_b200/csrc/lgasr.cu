@@ -55,7 +55,8 @@ struct lgasr_handle {
   int fused;         // 1: one k_step launch per position; 0: k_score_rows + k_select
   int cluster;       // 1: k_step is launched as clusters of `beam` CTAs (records through distributed shared memory)
   int seq_ok;        // 1: the whole grid of k_step is one wave, replay positions use the SEQ instance
-  int v2;            // 1: k_step2 (second-generation step kernel) runs the position; 0: k_step (LGASR_V1=1)
+  int v2;            // 1: k_step2 is available for this handle (geometry computed)
+  int v2_all;        // 1: every fused launch takes k_step2 (LGASR_V2=1); 0: only bf16 / normalised term matrices do
   StepLaunch sl2;    // k_step2 launch geometry
   size_t smem_step2;
   int cluster2;      // k_step2 launched as clusters of `beam` CTAs
@@ -434,8 +435,11 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
   }
   // ---- k_step2 geometry: 6 scan rows of Tp + 4 floats, arena = pending keys | candidate rows | selection scratch ----
   {
-    const char* v2 = getenv("LGASR_V2");  // work in progress: k_step2 is opt-in until it beats k_step
-    h->v2 = h->fused && (v2 && v2[0] == '1');
+    // k_step2 serves the term matrices k_step cannot read (bf16 storage, per-row normalisers: lgasr_step_ex);
+    // LGASR_V2=1 routes every fused launch through it (it is a little slower than k_step on plain fp32 matrices)
+    const char* v2 = getenv("LGASR_V2");
+    h->v2_all = (v2 && v2[0] == '1') ? 1 : 0;
+    h->v2 = h->fused ? 1 : 0;
     if (h->v2) {
       StepLaunch& sl = h->sl2;
       sl = h->sl;
@@ -466,7 +470,7 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       // threads per CTA: the glue is paid per warp, so large grids (several waves) take fewer, fatter warps
       {
         const char* nt = getenv("LGASR_NTH");
-        h->nth2 = 128;
+        h->nth2 = 128;  // measured: 128 threads per CTA beat 256 and 64 on the stepping launches (profiles/r02e)
         if (nt && (atoi(nt) == 64 || atoi(nt) == 128 || atoi(nt) == 256)) h->nth2 = atoi(nt);
       }
       const void* fns[8];
@@ -635,13 +639,19 @@ extern "C" int lgasr_begin(lgasr_handle* h, const int32_t* h_maxlen, const int32
   return LGASR_OK;
 }
 
-static int fill_terms(lgasr_handle* h, Terms& tm, const float* const* ptr, const float* cst, const float* w, int64_t ld) {
+static int fill_terms(lgasr_handle* h, Terms& tm, const float* const* ptr, const float* cst, const float* w, int64_t ld,
+                      const int32_t* dtype = nullptr, const float* const* norm = nullptr) {
   Dev& d = h->d;
   memset(&tm, 0, sizeof(tm));
   tm.K = d.K;
   tm.ld = ld;
   for (int k = 0; k < d.K; ++k) {
     tm.ptr[k] = ptr ? ptr[k] : nullptr;
+    if (tm.ptr[k] && dtype) {
+      if (dtype[k] != LGASR_F32 && dtype[k] != LGASR_BF16) return fail(LGASR_EINVAL, "term %d: unknown dtype %d", k, dtype[k]);
+      tm.bf16[k] = dtype[k] == LGASR_BF16 ? 1 : 0;
+    }
+    tm.norm[k] = (tm.ptr[k] && norm) ? norm[k] : nullptr;
     tm.cst[k] = cst ? cst[k] : 0.f;
     tm.w[k] = w ? w[k] : 0.f;
     tm.slot[k] = tm.nptr;
@@ -676,7 +686,7 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     return fail(LGASR_EINVAL, "bf16 / normalised term matrices need 16-byte aligned rows, V %% 4 == 0 and the fused step");
   if (!plain && d.key >= 0 && (tm.bf16[d.key] || tm.norm[d.key]))
     return fail(LGASR_EINVAL, "the pre-beam key term must be a plain fp32 log-probability matrix");
-  if (h->v2 && al) {
+  if (h->v2 && al && (h->v2_all || !plain)) {
     StepLaunch sl = h->sl2;
     sl.tma_rows = 1;
     sl.row_path = (d.key >= 0) ? 1 : (plain && tm.K == 1 && tm.nptr == 1) ? 1 : (plain && tm.K == 2 && tm.nptr == 2) ? 2 : 0;
@@ -801,10 +811,21 @@ extern "C" int lgasr_step(lgasr_handle* h, const float* const* h_term_ptr, const
   return step_impl(h, tm, (cudaStream_t)stream);
 }
 
+extern "C" int lgasr_step_ex(lgasr_handle* h, const void* const* h_term_ptr, const int32_t* h_term_dtype,
+                             const float* const* h_term_norm, const float* h_term_const, const float* h_term_weight, int64_t ld,
+                             void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  if (!h->begun) return fail(LGASR_ESTATE, "lgasr_step_ex before lgasr_begin");
+  Terms tm;
+  TRY(fill_terms(h, tm, reinterpret_cast<const float* const*>(h_term_ptr), h_term_const, h_term_weight, ld, h_term_dtype,
+                 h_term_norm));
+  return step_impl(h, tm, (cudaStream_t)stream);
+}
+
 extern "C" int lgasr_launch_info(lgasr_handle* h, int32_t* cluster, int32_t* smem_bytes, int32_t* chunk_floats, int32_t* stages) {
   if (!h) return fail(LGASR_EINVAL, "null handle");
-  if (cluster) *cluster = h->v2 ? h->cluster2 : (h->fused ? h->cluster : 0);
-  if (smem_bytes) *smem_bytes = (int32_t)(h->v2 ? h->smem_step2 : (h->fused ? h->smem_step : h->smem_rows));
+  if (cluster) *cluster = h->v2_all ? h->cluster2 : (h->fused ? h->cluster : 0);
+  if (smem_bytes) *smem_bytes = (int32_t)(h->v2_all ? h->smem_step2 : (h->fused ? h->smem_step : h->smem_rows));
   if (chunk_floats) *chunk_floats = h->sl.CH;
   if (stages) *stages = h->sl.NST;
   return LGASR_OK;
@@ -1280,7 +1301,7 @@ extern "C" int lgasr_reorder_rows(lgasr_handle* h, void* d_dst, const void* d_sr
 
 template <bool BF16, bool VECIO>
 static int launch_lsm(const void* logits, long long ld_in, float* out, long long ld_out, int rows, int V, int SL, int CS,
-                      cudaStream_t st) {
+                      cudaStream_t st, float* lse_out) {
   auto kern = k_log_softmax_rows<BF16, VECIO>;
   const size_t smem = (size_t)SL * (BF16 ? 2 : 4);
   if (smem > 48 * 1024) {
@@ -1299,15 +1320,15 @@ static int launch_lsm(const void* logits, long long ld_in, float* out, long long
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, logits, ld_in, out, ld_out, V, SL);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, logits, ld_in, out, ld_out, V, SL, lse_out);
   if (e != cudaSuccess) return fail(LGASR_ECUDA, "%s", cudaGetErrorString(e));
   g_launches.fetch_add(1);
   return LGASR_OK;
 }
 
-extern "C" int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t ld_in, float* d_out, int64_t ld_out, int rows,
-                                      int vocab, void* stream) {
-  if (!d_logits || !d_out || rows < 0 || rows > 65535 || vocab < 1 || ld_in < vocab || ld_out < vocab ||
+static int lsm_impl(const void* d_logits, int dtype, int64_t ld_in, float* d_out, int64_t ld_out, float* d_lse, int rows,
+                    int vocab, void* stream) {
+  if (!d_logits || (!d_out && !d_lse) || rows < 0 || rows > 65535 || vocab < 1 || ld_in < vocab || (d_out && ld_out < vocab) ||
       (dtype != LGASR_F32 && dtype != LGASR_BF16))
     return fail(LGASR_EINVAL, "bad argument");
   if (rows == 0) return LGASR_OK;
@@ -1320,13 +1341,25 @@ extern "C" int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t l
   SL = (SL + 7) & ~7;  // slices start on 32-byte boundaries of the fp32 row (16-byte of a bf16 row)
   const bool bf = dtype == LGASR_BF16;
   const int vq = bf ? 8 : 4;
-  const bool vec = (vocab % vq) == 0 && (ld_in % vq) == 0 && (ld_out % 4) == 0 && (((uintptr_t)d_logits) & 15) == 0 &&
-                   (((uintptr_t)d_out) & 15) == 0;
+  const bool vec = (vocab % vq) == 0 && (ld_in % vq) == 0 && (!d_out || (ld_out % 4) == 0) && (((uintptr_t)d_logits) & 15) == 0 &&
+                   (!d_out || (((uintptr_t)d_out) & 15) == 0);
   cudaStream_t st = (cudaStream_t)stream;
-  if (bf) return vec ? launch_lsm<true, true>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st)
-                     : launch_lsm<true, false>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st);
-  return vec ? launch_lsm<false, true>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st)
-             : launch_lsm<false, false>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st);
+  if (bf) return vec ? launch_lsm<true, true>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st, d_lse)
+                     : launch_lsm<true, false>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st, d_lse);
+  return vec ? launch_lsm<false, true>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st, d_lse)
+             : launch_lsm<false, false>(d_logits, ld_in, d_out, ld_out, rows, vocab, SL, CS, st, d_lse);
+}
+
+extern "C" int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t ld_in, float* d_out, int64_t ld_out, int rows,
+                                      int vocab, void* stream) {
+  if (!d_out) return fail(LGASR_EINVAL, "bad argument");
+  return lsm_impl(d_logits, dtype, ld_in, d_out, ld_out, nullptr, rows, vocab, stream);
+}
+
+extern "C" int lgasr_row_logsumexp(const void* d_logits, int dtype, int64_t ld_in, float* d_lse, int rows, int vocab,
+                                   void* stream) {
+  if (!d_lse) return fail(LGASR_EINVAL, "bad argument");
+  return lsm_impl(d_logits, dtype, ld_in, nullptr, 0, d_lse, rows, vocab, stream);
 }
 
 extern "C" int lgasr_score_filter(const int64_t* d_yseq, int64_t ld_y, int cur_len, int rows, int vocab, int notimestamps,

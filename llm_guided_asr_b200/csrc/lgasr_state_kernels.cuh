@@ -106,8 +106,11 @@ struct LsmIn<true> {
 // BF16: logits are bf16.  VECIO: V, SL, both leading dimensions and both pointers allow 16-byte accesses;
 // the slice then arrives by kLsmChunks 1-D TMA bulk copies (cp.async.bulk + mbarrier), else by plain loads.
 template <bool BF16, bool VECIO>
+// out may be NULL (normaliser only); lse_out (may be NULL) receives the row's logsumexp: lgasr_step_ex then reads the
+// LOGITS once, in their own type, and subtracts the normaliser in registers.
 __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __restrict__ logits, long long ld_in,
-                                                                  float* __restrict__ out, long long ld_out, int V, int SL) {
+                                                                  float* __restrict__ out, long long ld_out, int V, int SL,
+                                                                  float* __restrict__ lse_out) {
   using In = LsmIn<BF16>;
   using T = typename In::T;
   constexpr int NV = In::kVec;
@@ -203,6 +206,8 @@ __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __
     s = S;
   }
   const float lse = m + logf(s);
+  if (lse_out && tid == 0 && c == 0) lse_out[r] = lse;
+  if (!out) return;
   float* o = out + r * ld_out + v0;
   if (VECIO) {
     for (int i = tid; i < nv; i += kLsmThreads) {

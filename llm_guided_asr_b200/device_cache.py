@@ -51,16 +51,41 @@ def log_softmax_rows(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -
     return out
 
 
+def row_logsumexp(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``logsumexp(logits, dim=-1)`` in fp32 for a ``(rows, V)`` fp32 or bf16 CUDA tensor, by ``lgasr_row_logsumexp``: the
+    per-row normaliser ``lgasr_step_ex`` subtracts while it reads the logits themselves (no ``(rows, V)`` fp32
+    log-probability matrix is ever written)."""
+    if logits.device.type != "cuda":
+        raise RuntimeError("row_logsumexp needs a CUDA tensor: there is no CPU fallback")
+    if logits.dim() != 2 or logits.stride(1) != 1 or logits.dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("row_logsumexp: (rows, V) fp32 / bf16 tensor with unit stride along V expected")
+    rows, V = logits.shape
+    if out is None:
+        out = torch.empty(rows, dtype=torch.float32, device=logits.device)
+    lib = _lib.load()
+    with torch.cuda.device(logits.device):
+        st = int(torch.cuda.current_stream(logits.device).cuda_stream)
+        ld_in = logits.stride(0) if rows > 1 else V
+        _lib.check(lib.lgasr_row_logsumexp(C.c_void_p(logits.data_ptr()), 1 if logits.dtype == torch.bfloat16 else 0, ld_in,
+                                           C.c_void_p(out.data_ptr()), rows, V, st))
+    return out
+
+
 class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
     """Machinery shared by the device-protocol scorers: static buffers per batch shape, one network call per
     position for all ``B*beam`` row slots (``_net``), ``lgasr_log_softmax_rows`` into the row layout of
     ``lgasr_step``, ``lgasr_reorder_rows`` of every layer's cache by the parents the step chose, optional CUDA-graph
     capture of the network call per prefix length."""
 
-    def __init__(self, net: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
+    def __init__(self, net: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False,
+                 fused_normaliser: bool = False):
         torch.nn.Module.__init__(self)
         self.net = net
         self.fused_log_softmax = fused_log_softmax
+        # fused_normaliser: hand the LOGITS (fp32 or bf16, as the network produced them) plus one logsumexp per row to
+        # the step (lgasr_row_logsumexp + lgasr_step_ex) instead of writing an fp32 (B*W, V) log-probability matrix:
+        # the step reads the row once, in its own type (2 bytes per entry for a bf16 LLM head)
+        self.fused_normaliser = fused_normaliser
         # cuda_graphs: the network call of a position (embed -> layers -> output layer -> log-softmax) is captured
         # once per prefix length into a CUDA graph over static buffers and replayed for every later batch of the
         # same shape: an eager step is ~25 launches per layer, i.e. launch-bound at beam-search sizes
@@ -108,7 +133,9 @@ class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
             self._shape = shape
             self._graphs, self._pool = {}, None
             self._tgt = torch.zeros(B * W, int(max_positions), dtype=torch.int64, device=dev)
-            self._out = torch.empty(B * W, engine.cfg.vocab, dtype=torch.float32, device=dev)
+            self._out = None if self.fused_normaliser and engine.cfg.vocab % 4 == 0 else torch.empty(
+                B * W, engine.cfg.vocab, dtype=torch.float32, device=dev)
+            self._lse = torch.empty(B * W, dtype=torch.float32, device=dev)
             self._buf = None  # [2] x (n_layers, B*W, cap, Dm), allocated on the first call (Dm known then)
         self._begin_inputs(xs, lens, B, W, T, dev, fresh_shape)
         self._eng = engine
@@ -128,20 +155,32 @@ class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
         else:
             cache = [self._buf[self._pp][i, :, : L - 1] for i in range(nl)]
         logits, new = self._net(tgt, cache)
-        if self.fused_log_softmax:
-            log_softmax_rows(logits if logits.dtype in (torch.float32, torch.bfloat16) else logits.float(), self._out)
+        if logits.dtype not in (torch.float32, torch.bfloat16):
+            logits = logits.float()
+        if self._out is None:  # fused normaliser: (logits, logsumexp) go to the step as they are
+            logits = logits.contiguous()
+            row_logsumexp(logits, self._lse)
+            self._ret = (logits, self._lse)
+        elif self.fused_log_softmax:
+            log_softmax_rows(logits, self._out)
+            self._ret = self._out
         else:
             self._out.copy_(torch.log_softmax(logits.float(), dim=-1))
+            self._ret = self._out
         return new
 
     def batch_score_padded(self, yseq: torch.Tensor, n_run, done) -> torch.Tensor:
-        """``yseq (B, W, L)`` int64 running prefixes (all row slots) -> ``(B*W, V)`` fp32 log-probabilities;
-        rows of slots that are not running hold values nobody reads."""
+        """``yseq (B, W, L)`` int64 running prefixes (all row slots) -> ``(B*W, V)`` fp32 log-probabilities, or (with
+        ``fused_normaliser``) the pair ``(logits (B*W, V) fp32 / bf16, logsumexp (B*W,) fp32)``; rows of slots that
+        are not running hold values nobody reads."""
         B, W, L = yseq.shape
         self._tgt[:, :L].copy_(yseq.reshape(B * W, L).clamp(0, self._V - 1))  # idle slots may hold stale ids
-        if not self.cuda_graphs or self._fresh or self._buf is None:
+        stateless = self._n_layers() == 0
+        if not self.cuda_graphs or self._fresh or (self._buf is None and not stateless):
             self._new = self._forward(L)
-            return self._out
+            if stateless:
+                self._fresh = False
+            return self._ret
         key = (L, self._pp)
         ent = self._graphs.get(key)
         if ent is None:
@@ -156,16 +195,17 @@ class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
                 new = self._forward(L)
             if self._pool is None:
                 self._pool = g.pool()
-            ent = self._graphs[key] = (g, new)
+            ent = self._graphs[key] = (g, new, self._ret)
         ent[0].replay()
         self._new = ent[1]
-        return self._out
+        self._ret = ent[2]
+        return self._ret
 
     def device_reorder(self) -> None:
         """Queue, right behind ``engine.step``, the gather of every layer's cache rows by the parents the step
         chose (``lgasr_reorder_rows``): afterwards slot ``j`` of utterance ``b`` holds its parent's history."""
         new = self._new
-        if new is None:
+        if not new:  # nothing to re-order (no call yet, or a stateless scorer that re-reads the whole prefix)
             return
         L, Dm = new[0].shape[1], new[0].shape[2]
         if self._buf is None:
@@ -191,11 +231,12 @@ class DeviceCachedDecoderScorer(_DeviceCachedScorer):
     protocol (e.g. under the reference's own search) it simply delegates to the wrapped decoder.
     """
 
-    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
+    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False,
+                 fused_normaliser: bool = False):
         for name in ("embed", "decoders", "output_layer"):
             if not hasattr(decoder, name):
                 raise TypeError(f"decoder has no attribute {name!r}: not a BaseTransformerDecoder-like module")
-        super().__init__(decoder, fused_log_softmax, cuda_graphs)
+        super().__init__(decoder, fused_log_softmax, cuda_graphs, fused_normaliser)
 
     @property
     def decoder(self):
@@ -240,13 +281,14 @@ class DeviceCachedLMScorer(_DeviceCachedScorer):
     ``Encoder.forward_one_step``, ``espnet/nets/pytorch_backend/transformer/encoder.py:353-379``).  Replaces the
     per-hypothesis state transposes of ``TransformerLM.batch_score`` (``:118-122,132``) the same way."""
 
-    def __init__(self, lm: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False):
+    def __init__(self, lm: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False,
+                 fused_normaliser: bool = False):
         for name in ("embed", "encoder", "decoder"):
             if not hasattr(lm, name):
                 raise TypeError(f"language model has no attribute {name!r}: not a TransformerLM-like module")
         if not hasattr(lm.encoder, "encoders"):
             raise TypeError("language model encoder has no attribute 'encoders'")
-        super().__init__(lm, fused_log_softmax, cuda_graphs)
+        super().__init__(lm, fused_log_softmax, cuda_graphs, fused_normaliser)
 
     @property
     def lm(self):
@@ -268,3 +310,93 @@ class DeviceCachedLMScorer(_DeviceCachedScorer):
         if getattr(enc, "normalize_before", False):
             xs = enc.after_norm(xs)
         return lm.decoder(xs[:, -1]), new
+
+
+class DevicePrefixLMScorer(_DeviceCachedScorer):
+    """Full scorer around a Hugging Face causal language model that re-reads the whole prefix at every position, the
+    way the reference's ``HuggingfaceOPTModel.batch_score`` does (``espnet2/lm/huggingface_pretrained_opt_lm.py:110-148``:
+    ``self.decoder(ys)`` without a cache, ``lm_head`` on the last position, ``log_softmax``).  Surface: ``lm.decoder``
+    (a ``transformers`` base model whose output has ``last_hidden_state``) and ``lm.lm_head``; ``hf_lm.HFPrefixLM`` wraps
+    OPT, GPT-2, Llama ... base models that way (GPT-2-small random-init is configs[2]'s shallow-fusion scorer).
+
+    Device protocol: ONE model call per position for all ``B*beam`` row slots (the reference: one per utterance),
+    nothing to re-order (stateless), logits handed over through ``lgasr_log_softmax_rows`` or, with
+    ``fused_normaliser``, as ``(logits, logsumexp)`` read once by the step in their own type."""
+
+    def __init__(self, lm: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False,
+                 fused_normaliser: bool = False):
+        for name in ("decoder", "lm_head"):
+            if not hasattr(lm, name):
+                raise TypeError(f"language model has no attribute {name!r}: not a HuggingfaceOPTModel-like module")
+        super().__init__(lm, fused_log_softmax, cuda_graphs, fused_normaliser)
+
+    def _n_layers(self) -> int:
+        return 0
+
+    def _net(self, tgt, cache):
+        out = self.net.decoder(tgt, use_cache=False, return_dict=True)
+        return self.net.lm_head(out.last_hidden_state[:, -1]), []
+
+
+class DeviceLLMGuidedDecoderScorer(_DeviceCachedScorer):
+    """Full scorer around the fork's ``LLMGuidedTransformerDecoder`` (``espnet2/asr/decoder/transformer_decoder.py:944-1237``),
+    its ``batch_score`` semantics (``:1115-1132`` -> ``forward_one_step`` ``:1064-1113``): the CTC greedy hypothesis of
+    the utterance prompts the LLM (``llm.forward_inference``), the LLM's hidden states of the response tokens go through
+    ``embed`` and the attention decoder layers over the encoder memory, ``output_layer`` gives logits over the LLM
+    vocabulary (32 k / 128 k entries).
+
+    Surface used: ``dec.ctc.argmax``, ``dec.llm.forward_inference(hyps, hyps_lengths, tgt, tgt_lengths) -> (out, lens)``,
+    ``dec.llm.start_of_response_token_id``, ``dec.embed``, ``dec.decoders`` (called on whole sequences, as the reference
+    does at ``:1098-1100``), ``dec.after_norm`` / ``normalize_before``, ``dec.output_layer``; optional
+    ``dec.ctc_tokenizer`` / ``ctc_token_id_converter`` (text prompts).
+
+    Device protocol: one call per position for all ``B*beam`` row slots of ALL utterances (every row carries its own
+    utterance's prompt; the reference handles one utterance at a time and keeps the prompt in ``self.hyp``), logits
+    through ``lgasr_log_softmax_rows`` or as ``(logits, logsumexp)`` with ``fused_normaliser`` - the hand-off SURVEY.md
+    7.3-8 asks for: the wide bf16 row is read once."""
+
+    def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False,
+                 fused_normaliser: bool = False):
+        for name in ("embed", "decoders", "output_layer", "llm", "ctc"):
+            if getattr(decoder, name, None) is None:
+                raise TypeError(f"decoder has no {name!r}: not a configured LLMGuidedTransformerDecoder")
+        super().__init__(decoder, fused_log_softmax, cuda_graphs, fused_normaliser)
+
+    def _n_layers(self) -> int:
+        return 0  # batch_score (use_cache False) keeps no state: the whole prefix is re-read
+
+    def _begin_inputs(self, xs, lens, B, W, T, dev, fresh_shape):
+        dec = self.net
+        if fresh_shape:
+            self._memory = xs[0].new_zeros(B * W, T, xs[0].shape[-1])
+        mem = self._memory.view(B, W, T, -1)
+        mem.zero_()
+        hyps = []
+        for b, x in enumerate(xs):
+            mem[b, :, : lens[b]] = x
+            lpz = dec.ctc.argmax(x.unsqueeze(0)).data  # :1071-1074: greedy CTC, collapse repeats, drop blanks
+            y_hat = torch.unique_consecutive(lpz[0])
+            hyp = y_hat[y_hat != 0]
+            if getattr(dec, "ctc_tokenizer", None) is not None:
+                hyp = dec.ctc_tokenizer.tokens2text(dec.ctc_token_id_converter.ids2tokens(hyp))
+            hyps.append(hyp)
+        self._hyps = [hyps[b] for b in range(B) for _ in range(W)]
+        text = getattr(dec, "ctc_tokenizer", None) is not None
+        self._hyp_lens = torch.tensor([-1 if text else int(h.shape[0]) for h in self._hyps], dtype=torch.int64, device=dev)
+        # the reference passes memory_mask None (:1099): every frame of the (single) utterance is attended.  In a batch
+        # the shorter utterances are padded, so their padding frames are masked out
+        ar = torch.arange(T, device=dev)
+        mask = ar[None, :] < torch.as_tensor(list(lens), device=dev)[:, None]
+        self._memory_mask = mask[:, None, None, :].expand(B, W, 1, T).reshape(B * W, 1, T) if min(lens) < T else None
+
+    def _net(self, tgt, cache):
+        dec = self.net
+        n, L = tgt.shape
+        tgt = tgt.clone()
+        tgt[:, 0] = dec.llm.start_of_response_token_id  # :1087
+        llm_out, _ = dec.llm.forward_inference(self._hyps, self._hyp_lens, tgt, tgt.new_full((n,), L))
+        tgt_mask = torch.ones(L, L, dtype=torch.bool, device=tgt.device).tril().unsqueeze(0)
+        x = dec.embed(llm_out)
+        x, _, _, _ = dec.decoders(x, tgt_mask, self._memory, self._memory_mask)
+        y = dec.after_norm(x[:, -1]) if getattr(dec, "normalize_before", False) else x[:, -1]
+        return dec.output_layer(y), []

@@ -116,26 +116,48 @@ class FusedStepEngine:
             )
 
     def _terms(self, mats, consts, weights):
-        ptrs, ld = [], None
+        ptrs, dts, ld = [], [], None
         for m in mats:
             if m is None:
                 ptrs.append(0)
+                dts.append(0)
                 continue
-            assert m.is_cuda and m.dtype == torch.float32 and m.dim() == 2 and m.stride(1) == 1 and m.shape[1] == self.V
+            assert m.is_cuda and m.dim() == 2 and m.stride(1) == 1 and m.shape[1] == self.V
+            assert m.dtype in (torch.float32, torch.bfloat16), "term matrices are fp32 or bf16"
             ml = m.stride(0) if m.shape[0] > 1 else self.V
             assert ld is None or ld == ml, "all term matrices must share one row stride"
             ld = ml
             ptrs.append(m.data_ptr())
-        return ptrs, (ld if ld is not None else self.V)
+            dts.append(1 if m.dtype == torch.bfloat16 else 0)
+        return ptrs, dts, (ld if ld is not None else self.V)
 
-    def step(self, mats: List[Optional[torch.Tensor]], consts: List[float], weights: List[float]):
-        """One decode position. ``mats[k]``: ``(B*beam, V)`` fp32 device matrix (row = utt*beam+slot)
-        or None for a constant term ``consts[k]``."""
-        ptrs, ld = self._terms(mats, consts, weights)
+    def step(self, mats: List[Optional[torch.Tensor]], consts: List[float], weights: List[float],
+             norms: Optional[List[Optional[torch.Tensor]]] = None):
+        """One decode position. ``mats[k]``: ``(B*beam, V)`` fp32 or bf16 device matrix (row = utt*beam+slot)
+        or None for a constant term ``consts[k]``.  ``norms[k]`` (optional): ``(B*beam,)`` fp32 per-row normaliser,
+        the score of an entry is ``float(mats[k][r, v]) - norms[k][r]`` (logits + logsumexp: ``lgasr_step_ex``)."""
+        ptrs, dts, ld = self._terms(mats, consts, weights)
+        typed = any(dts) or (norms is not None and any(n is not None for n in norms))
         with torch.cuda.device(self.device):
+            if not typed:
+                _lib.check(
+                    self.lib.lgasr_step(
+                        self._h, _lib.ptr_array(ptrs), _lib.f32_array(consts), _lib.f32_array(weights), ld, _stream_ptr(self.device)
+                    )
+                )
+                return
+            nps = []
+            for k, m in enumerate(mats):
+                n = None if norms is None else norms[k]
+                if n is None or m is None:
+                    nps.append(0)
+                    continue
+                assert n.is_cuda and n.dtype == torch.float32 and n.is_contiguous() and n.numel() == self.B * self.beam
+                nps.append(n.data_ptr())
             _lib.check(
-                self.lib.lgasr_step(
-                    self._h, _lib.ptr_array(ptrs), _lib.f32_array(consts), _lib.f32_array(weights), ld, _stream_ptr(self.device)
+                self.lib.lgasr_step_ex(
+                    self._h, _lib.ptr_array(ptrs), _lib.i32_array(dts), _lib.ptr_array(nps), _lib.f32_array(consts),
+                    _lib.f32_array(weights), ld, _stream_ptr(self.device),
                 )
             )
 
@@ -145,6 +167,7 @@ class FusedStepEngine:
         flat = []
         for row in mats_per_step:
             for m in row:
+                assert m is None or m.dtype == torch.float32, "replay takes fp32 matrices (typed terms: step)"
                 flat.append(0 if m is None else m.data_ptr())
         with torch.cuda.device(self.device):
             _lib.check(
