@@ -355,6 +355,166 @@ def roofline_b512(dev, cfg, peak, reps=3):
     }
 
 
+def run_configs4(rank, world, dev, cfg, n_utts=4096, batch=512, K=2, reps=2):
+    """BASELINE.json configs[4]: 4096 synthetic utterances (conformer + LM fusion: two full-scorer matrices, beam 10),
+    utterance-sharded over the ranks through the product driver (sharding.partition / batches / decode_sharded, one
+    lock-step batch of up to 512 utterances per handle, length-bucketed; jittered lengths F in [1200, 1500] frames ->
+    T in [299, 374]).  STRONG scaling: the total work is fixed.  Posteriors and matrices are resident (generated on the
+    device before the clock starts); the final hypothesis gather (NCCL) is inside the timed region."""
+    from llm_guided_asr_b200 import sharding
+    from llm_guided_asr_b200.engine import FusedStepEngine
+
+    T, V, W, L = cfg["T"], cfg["V"], cfg["beam"], cfg["L"]
+    eos = V - 1
+    rng = np.random.default_rng(4)
+    F = rng.integers(1200, 1501, size=n_utts)
+    lengths = [int(((f - 1) // 2 - 1) // 2) for f in F]  # conv2d x4 subsampling (SURVEY.md 8)
+    mine = sharding.partition(lengths, world)[rank]
+    my_batches = sharding.batches(mine, lengths, batch)
+    g = torch.Generator(device=dev).manual_seed(40 + rank)
+    tabs = [torch.log_softmax(2.0 * torch.randn(L, batch * W, V, device=dev, generator=g), dim=-1) for _ in range(K)]
+    logps = {}
+    for bi, idx in enumerate(my_batches):  # posteriors of this rank's utterances, resident before the clock starts
+        logps[bi] = torch.log_softmax(3.0 * torch.randn(len(idx), T, V, device=dev, generator=g), dim=-1)
+    engines = {}
+    wts, consts = [0.7, 0.5][:K], [0.0] * K
+    names = ["decoder", "lm"][:K]
+    pos = {tuple(idx): bi for bi, idx in enumerate(my_batches)}
+
+    def decode_fn(idx):
+        bi = pos[tuple(idx)]
+        Bb = len(idx)
+        eng = engines.get(Bb)
+        if eng is None:
+            eng = engines[Bb] = FusedStepEngine(Bb, T, V, W, cfg["S"], names, "full", True, cfg["ctc_weight"], eos, eos, L, 1,
+                                                False, device=dev)
+        eng.set_posteriors(logps[bi], [lengths[i] for i in idx])
+        eng.begin([L] * Bb, [0] * Bb, [eos])
+        eng.replay([[t[i][: Bb * W] for t in tabs] for i in range(L)], consts, wts, ld=V)
+        return eng.gather_best()
+
+    times = []
+    merged = None
+    for _ in range(reps + 1):
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        merged = sharding.decode_sharded(decode_fn, lengths, batch, rank=rank, world=world)
+        torch.cuda.synchronize(dev)
+        times.append(time.perf_counter() - t0)
+    t = torch.tensor([min(times[1:])], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    for e in engines.values():
+        e.close()
+    del tabs, logps
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    sec = float(t[0])
+    ok = merged is not None and [r[0] for r in merged] == list(range(n_utts)) and all(len(r[1]) == L + 2 for r in merged)
+    summ = sharding.shard_summary(lengths, world)
+    return {
+        "workload": f"configs[4]: {n_utts} synthetic utterances, T in [299, 374] (jittered), V={V}, beam={W}, pre-beam={cfg['S']}, {K} full-scorer matrices, {L} positions, batches of <= {batch} utterances per handle",
+        "value": n_utts / sec, "unit": "utts/s", "scaling": "strong", "seconds": sec, "n_gpus": world,
+        "utts_per_rank": summ["count"], "frames_per_rank": summ["frames"],
+        "all_utterances_returned_in_order": bool(ok),
+        "through": "sharding.partition / batches / decode_sharded -> FusedStepEngine.set_posteriors / begin / replay / gather_best; final gather of (index, tokens, score) records to rank 0 inside the timed region",
+    }
+
+
+def run_decode_real(dev, cfg, reps=3):
+    """A neural scorer in the timed loop (rank 0, one GPU): BatchBeamSearch.decode_batch at configs[1] size with the
+    conformer recipe's attention decoder (6 blocks, 512 wide, 8 heads, 2048 feed-forward, random-init; the reference's own
+    TransformerDecoder class when baseline/_ref is present) behind DeviceCachedDecoderScorer (all 640 row slots in one call
+    per position, caches re-ordered on the device, CUDA graphs, memory keys / values projected once per utterance), a
+    512 -> 5000 CTC head, 64 positions.  Wall clock around decode_batch (synchronised), best of `reps` after a warm-up."""
+    from baseline import ref_harness as rh
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer
+    from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer
+
+    B, T, V, W, L, D = cfg["B"], cfg["T"], cfg["V"], cfg["beam"], cfg["L"], 512
+    eos = V - 1
+    g = torch.Generator().manual_seed(0)
+    xs = [torch.randn(T, D, generator=g).to(dev) for _ in range(B)]
+    torch.manual_seed(0)
+    kind = "TinyDecoder (llm_guided_asr_b200.testing), generic layers"
+    dec = None
+    if rh.available():
+        try:
+            rh.activate()
+            from espnet2.asr.decoder.transformer_decoder import TransformerDecoder
+
+            dec = TransformerDecoder(V, D, attention_heads=8, linear_units=2048, num_blocks=6, dropout_rate=0.0,
+                                     positional_dropout_rate=0.0, self_attention_dropout_rate=0.0, src_attention_dropout_rate=0.0)
+            kind = "reference TransformerDecoder (baseline/_ref), random-init"
+        except Exception:
+            dec = None
+    if dec is None:
+        from llm_guided_asr_b200.testing import synthetic as syn
+
+        dec = syn.TinyDecoder(V, D=D, layers=6, heads=8, ff=2048, seed=1)
+    dec = dec.eval().to(dev)
+
+    class ProjCTC(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            torch.manual_seed(2)
+            self.lo = torch.nn.Linear(D, V)
+
+        def log_softmax(self, hs):
+            return torch.log_softmax(self.lo(hs), dim=-1)
+
+    ctc = ProjCTC().eval().to(dev)
+    out = {"decoder": kind, "B": B, "T": T, "V": V, "beam": W, "positions": L,
+           "note": "fp32 = the reference's arithmetic (torch fp32 matmul, TF32 off); tf32 / bf16 are the caller's choice of network precision: "
+                   "the search, the CTC recursion and the fusion stay fp32; bf16 hands (logits, logsumexp) to the step (lgasr_step_ex)"}
+    import copy
+
+    variants = (
+        ("fp32", dict(cuda_graphs=True), torch.float32, False),
+        ("tf32", dict(cuda_graphs=True), torch.float32, True),
+        ("bf16_fused_normaliser", dict(cuda_graphs=True, fused_normaliser=True), torch.bfloat16, False),
+    )
+    for name, kw, dt, tf32 in variants:
+        old_tf32 = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+        try:
+            net = dec if dt == torch.float32 else copy.deepcopy(dec).to(dt)
+            xin = xs if dt == torch.float32 else [x.to(dt) for x in xs]
+
+            class CastCTC(torch.nn.Module):  # the CTC head stays fp32 whatever the decoder runs in
+                def log_softmax(self, hs):
+                    return ctc.log_softmax(hs.float())
+
+            sc = DeviceCachedDecoderScorer(net, **kw)
+            bs = BatchBeamSearch(scorers=dict(decoder=sc, ctc=CTCPrefixScorer(ctc=CastCTC(), eos=eos)),
+                                 weights=dict(decoder=1.0 - cfg["ctc_weight"], ctc=cfg["ctc_weight"]), beam_size=W, vocab_size=V,
+                                 sos=eos, eos=eos, pre_beam_score_key="full")
+            best = 1e9
+            with torch.no_grad():
+                for it in range(reps + 1):
+                    bs.collect_timing = it == reps
+                    torch.cuda.synchronize(dev)
+                    t0 = time.perf_counter()
+                    res = bs.decode_batch(xin, -float(L), 0.0)
+                    torch.cuda.synchronize(dev)
+                    if it and not bs.collect_timing:
+                        best = min(best, time.perf_counter() - t0)
+            tm = bs.last_timing
+            out[name] = {
+                "ms_per_batch": best * 1e3, "utts_per_sec": B / best, "ms_per_position": best * 1e3 / bs.last_steps,
+                "positions_run": bs.last_steps, "hyps_first_utt": len(res[0]),
+                "split_ms_per_position": {k: tm[k] / max(tm["positions"], 1) for k in ("scorers", "step", "reorder")},
+            }
+            del sc, bs
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = old_tf32
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     from llm_guided_asr_b200 import _lib
     from llm_guided_asr_b200.engine import FusedStepEngine
@@ -471,6 +631,10 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms_total, e2e_ms = float(t[0]), float(t[1])
+    # configs[4]: the 4096-utterance sweep through the sharded product driver (every rank takes part)
+    del d_tables, h_tables, mats_dev, mats_host
+    torch.cuda.empty_cache()
+    c4 = None if args.no_configs4 else run_configs4(rank, world, dev, cfg)
     ms_step = ms_total / args.steps
     value = world * B / (ms_step * 1e-3)
     e2e_val = world * B / (e2e_ms / args.steps * 1e-3)
@@ -478,9 +642,13 @@ def run_ours(args, rank, world, local_rank):
         return
 
     # ---- rank 0, one GPU: the reference itself beside it (CPU on all host cores, GPU PyTorch) + parity ----------
-    cpu = parity = ref_gpu = b512 = None
+    cpu = parity = ref_gpu = b512 = real = None
     if args.gpus == 1 and not args.no_cpu:
         b512 = roofline_b512(dev, cfg, peak)
+        try:
+            real = run_decode_real(dev, cfg)
+        except Exception as e:  # informative leg: never fail the bench line on it
+            real = {"unavailable": repr(e)[:300]}
         cores = os.cpu_count() or 1
         # the whole batch through the reference on the host cores (about 64 / cores x 2 s)
         dt, rres, kind = reference_cpu_run(logp, tables, cfg, list(range(B)), L, cores)
@@ -553,6 +721,8 @@ def run_ours(args, rank, world, local_rank):
                        "algorithmic_bytes_per_launch": ab_rep},
         },
         "roofline_b512": b512,
+        "configs4": c4,
+        "decode_real": real,
         "cpu_baseline": cpu,
         "reference_gpu": ref_gpu,
         "parity": parity,
@@ -568,6 +738,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference_gpu"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / parity leg")
+    ap.add_argument("--no-configs4", action="store_true", help="skip the 4096-utterance sharded sweep")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -88,6 +88,15 @@ int lgasr_set_posteriors_host(lgasr_handle* h, const float* h_logp, const int32_
 int lgasr_begin(lgasr_handle* h, const int32_t* h_maxlen, const int32_t* h_minlen,
                 const int64_t* h_primer, void* stream);
 
+/* Continuous batching (SURVEY.md 7.3-6, 8e "continuous refill"): utterance slot `utt` of a running handle, whose previous
+ * utterance has finished (done flag of lgasr_poll; read its n-best with lgasr_gather_ended first), takes a NEW utterance:
+ * d_logp [T][V] fp32 log-posteriors of that utterance alone (T = max_frames of the handle; frames >= xlen are padded as
+ * ctc_prefix_score.py:46-49), its length bounds, the handle's primer.  The other slots are untouched: every slot is at
+ * its own decode position (the kernels derive it from the slot's prefix length).  Replaces starting a new
+ * CTCPrefixScoreTH / init_hyp for the next utterance (scorers/ctc.py:87-99, batch_beam_search.py:130-159) while the rest
+ * of the batch keeps decoding.  The reference decodes strictly one utterance at a time (asr_inference.py:759-764). */
+int lgasr_refill(lgasr_handle* h, int utt, const float* d_logp, int xlen, int maxlen, int minlen, void* stream);
+
 /* One decode position for every unfinished utterance = BatchBeamSearch.search + post_process +
  * end_detect (batch_beam_search.py:259-429, e2e_asr_common.py:17-48) with the CTC prefix
  * recursion of CTCPrefixScoreTH.__call__ / select_state (ctc_prefix_score.py:67-187,

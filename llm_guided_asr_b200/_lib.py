@@ -51,6 +51,7 @@ PROTOTYPES = {
     "lgasr_set_posteriors": (_I, [_P, _P, _PI32, _P]),
     "lgasr_set_posteriors_host": (_I, [_P, _P, _PI32, _P]),
     "lgasr_begin": (_I, [_P, _PI32, _PI32, _PI64, _P]),
+    "lgasr_refill": (_I, [_P, _I, _P, _I, _I, _I, _P]),
     "lgasr_step": (_I, [_P, C.POINTER(_P), _PF, _PF, _I64, _P]),
     "lgasr_view": (_I, [_P, _I, C.POINTER(_P), C.POINTER(_I64)]),
     "lgasr_poll": (_I, [_P, _PI32, _PI32, _PI32, _PI32, _PI32, _P]),

@@ -119,6 +119,12 @@ class BatchBeamSearch(torch.nn.Module):
         self.normalize_length = normalize_length
         self._engines: "OrderedDict[tuple, FusedStepEngine]" = OrderedDict()
         self.last_steps = 0  # decode positions executed by the last call
+        # poll_every: positions between two host reads of the done flags when every full scorer keeps its state on the
+        # device (nothing on the host depends on the step's outcome then; positions run past an utterance's end cost
+        # idle CTAs only).  None: 1 with end detection (maxlenratio == 0), 8 otherwise.
+        self.poll_every: Optional[int] = None
+        self.collect_timing = False  # True: CUDA-event split of decode_batch into scorer calls / step / reorder
+        self.last_timing: Dict[str, float] = {}
 
     def set_hyp_primer(self, hyp_primer: List[int] = None) -> None:
         self.hyp_primer = hyp_primer
@@ -168,6 +174,123 @@ class BatchBeamSearch(torch.nn.Module):
             raise NotImplementedError("sequential attention (pre_x) is outside the fused path")
         return self.decode_batch([x], maxlenratio, minlenratio)[0]
 
+    def _hyps_of(self, eng, b, out_names, device) -> List[Hypothesis]:
+        """N-best list of slot ``b`` (ended hypotheses, best first; ``beam_search.py:452-459``)."""
+        toks, score, scores = eng.gather_ended(b)
+        hyps = [
+            Hypothesis(
+                yseq=torch.tensor(t, dtype=torch.int64, device=device),
+                score=torch.tensor(float(score[e]), dtype=torch.float32, device=device),
+                scores={k: torch.tensor(float(scores[e, j]), device=device) for j, k in enumerate(out_names)},
+                states={},
+            )
+            for e, t in enumerate(toks)
+        ]
+        keys = [float(score[e]) / (len(t) - 1) if self.normalize_length else float(score[e]) for e, t in enumerate(toks)]
+        return [hyps[i] for i in sorted(range(len(hyps)), key=lambda i: keys[i], reverse=True)]
+
+    @torch.no_grad()
+    def decode_stream(
+        self, xs: Sequence[torch.Tensor], slots: int, maxlenratio: float = 0.0, minlenratio: float = 0.0
+    ) -> List[List[Hypothesis]]:
+        """Continuous batching: ``len(xs)`` utterances through ``slots`` lock-step slots; the moment an utterance ends
+        (``done`` flag of the step: end detection, no running hypothesis left, or its maximum length) its slot is
+        handed to the next utterance of the list (``lgasr_refill``) while the others keep decoding, so no slot idles
+        behind the longest utterance of a batch.  Per utterance identical to ``forward``.
+
+        Full scorers are driven through the plain ``BatchScorerInterface`` protocol, one call per utterance and
+        position (the slots are at different prefix lengths)."""
+        n_utt = len(xs)
+        if n_utt == 0:
+            return []
+        B = min(int(slots), n_utt)
+        device = xs[0].device
+        if device.type != "cuda":
+            raise RuntimeError("BatchBeamSearch (fused, sm_100a) needs CUDA tensors: there is no CPU fallback")
+        lens = [int(x.shape[0]) for x in xs]
+        bounds = [length_bounds(t, maxlenratio, minlenratio) for t in lens]
+        primer = [self.sos] if self.hyp_primer is None else list(self.hyp_primer)
+        P = len(primer)
+        eng = self._engine(B, max(lens), max(b[0] for b in bounds), P, maxlenratio == 0.0, device)
+        W, V = self.beam_size, self.n_vocab
+        ctc_name = next(iter(self.part_scorers), None)
+        ctc = self.part_scorers[ctc_name].ctc if ctc_name is not None else None
+
+        def posteriors(u):
+            lp = torch.empty(eng.T, V, dtype=torch.float32, device=device)
+            lp[: lens[u]] = ctc.log_softmax(xs[u].unsqueeze(0))[0].to(torch.float32)
+            return lp
+
+        slot_utt = list(range(B))  # utterance held by each slot
+        nxt = B
+        if ctc is not None:
+            eng.set_posteriors(torch.stack([posteriors(u) for u in slot_utt]), [lens[u] for u in slot_utt])
+        else:
+            eng.set_posteriors(None, [lens[u] for u in slot_utt])
+        eng.begin([bounds[u][0] for u in slot_utt], [bounds[u][1] for u in slot_utt], primer)
+        names = list(self.full_scorers)
+        wts = [float(self.weights[k]) for k in names]
+        out_names = names + ([ctc_name] if ctc_name is not None else [])
+        states = {k: [[self.full_scorers[k].batch_init_state(xs[u])] for u in slot_utt] for k in names}
+        n_run, done, cur_len = [1] * B, [0] * B, [P] * B
+        pad = {k: None for k in names}
+        results: List[Optional[List[Hypothesis]]] = [None] * n_utt
+        steps = 0
+        while True:
+            yseq = eng.view(0)
+            mats, consts = [], []
+            new_states = {k: [None] * B for k in names}
+            for k in names:
+                d = self.full_scorers[k]
+                if getattr(d, "constant_score", None) is not None:
+                    mats.append(None)
+                    consts.append(float(d.constant_score))
+                    continue
+                if pad[k] is None:
+                    pad[k] = torch.zeros(B * W, V, dtype=torch.float32, device=device)
+                for b in range(B):
+                    if done[b] or n_run[b] == 0:
+                        continue
+                    u = slot_utt[b]
+                    ys = yseq[b, : n_run[b], : cur_len[b]]
+                    sc, st = d.batch_score(ys, states[k][b], xs[u].expand(n_run[b], *xs[u].shape))
+                    new_states[k][b] = st
+                    pad[k][b * W : b * W + n_run[b]] = sc
+                mats.append(pad[k])
+                consts.append(0.0)
+            eng.step(mats, consts, wts)
+            steps += 1
+            nrun_new, done_new, par, _tok, _act = eng.poll(with_parents=True)
+            for b in range(B):
+                if done[b]:
+                    continue
+                cur_len[b] += 1
+                for k in names:
+                    d = self.full_scorers[k]
+                    if new_states[k][b] is not None:
+                        states[k][b] = [d.select_state(new_states[k][b], int(par[b, r])) for r in range(int(nrun_new[b]))]
+                n_run[b] = int(nrun_new[b])
+                if int(done_new[b]):
+                    u = slot_utt[b]
+                    hyps = self._hyps_of(eng, b, out_names, device)
+                    if len(hyps) == 0 and minlenratio >= 0.1:  # beam_search.py:462-471
+                        hyps = self.decode_batch([xs[u]], maxlenratio, max(0.0, minlenratio - 0.1))[0]
+                    results[u] = hyps
+                    if nxt < n_utt:  # the slot takes the next utterance at once
+                        u2 = nxt
+                        nxt += 1
+                        eng.refill(b, posteriors(u2) if ctc is not None else None, lens[u2], bounds[u2][0], bounds[u2][1])
+                        slot_utt[b] = u2
+                        for k in names:
+                            states[k][b] = [self.full_scorers[k].batch_init_state(xs[u2])]
+                        n_run[b], cur_len[b] = 1, P
+                    else:
+                        done[b] = 1
+            if all(done):
+                break
+        self.last_steps = steps
+        return results
+
     @torch.no_grad()
     def decode_batch(
         self, xs: Sequence[torch.Tensor], maxlenratio: float = 0.0, minlenratio: float = 0.0
@@ -214,9 +337,21 @@ class BatchBeamSearch(torch.nn.Module):
         done = [0] * B
         pad = {k: None for k in names}
         steps = 0
+        all_device = len(padded) + sum(1 for k in names if getattr(self.full_scorers[k], "constant_score", None) is not None) == len(names)
+        every = self.poll_every if self.poll_every is not None else (1 if maxlenratio == 0.0 else 8)
+        every = max(1, every) if all_device else 1
+        ev = [] if self.collect_timing else None
+
+        def mark(tag):
+            if ev is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                ev.append((tag, e))
+
         for i in range(max(maxlen)):
             cur_len = len(primer) + i
             yseq = eng.view(0)  # (B, W, Lcap) current running prefixes
+            mark("start")
             mats, consts, norm_at = [], [], {}
             new_states = {k: [None] * B for k in names}
             for k in names:
@@ -268,11 +403,16 @@ class BatchBeamSearch(torch.nn.Module):
                 else:
                     mats.append(pad[k])
                     consts.append(0.0)
+            mark("scorers")
             eng.step(mats, consts, wts, [norm_at.get(j) for j in range(len(mats))] if norm_at else None)
+            mark("step")
             steps += 1
             for k in names:  # device-resident caches: parent-indexed gather queued behind the step
                 if hasattr(self.full_scorers[k], "device_reorder"):
                     self.full_scorers[k].device_reorder()
+            mark("reorder")
+            if all_device and (i + 1) % every != 0 and i + 1 < max(maxlen):
+                continue  # no host read this position: the next scorer call is queued right behind the gather
             nrun_new, done_new, par, _tok, n_active = eng.poll(with_parents=len(padded) < len(names))
             # re-order the full scorers' states by the parent slots (batch_beam_search.py:347-351)
             for k in names:
@@ -289,24 +429,51 @@ class BatchBeamSearch(torch.nn.Module):
             if n_active == 0:
                 break
         self.last_steps = steps
+        if ev is not None:
+            torch.cuda.synchronize(device)
+            acc = {"scorers": 0.0, "step": 0.0, "reorder": 0.0}
+            for (t0, e0), (t1, e1) in zip(ev, ev[1:]):
+                if t1 in acc:
+                    acc[t1] += e0.elapsed_time(e1)
+            self.last_timing = dict(acc, positions=steps)
 
         results = []
         out_names = names + ([ctc_name] if ctc_name is not None else [])
+        # every hypothesis of the batch in THREE host->device copies (tokens, scores, per-scorer scores); the Hypothesis
+        # fields are views of those tensors
+        gathered = [eng.gather_ended(b) for b in range(B)]
+        flat_tok = [t for toks, _, _ in gathered for seq in toks for t in seq]
+        tok_dev = torch.tensor(flat_tok, dtype=torch.int64, device=device) if flat_tok else torch.zeros(0, dtype=torch.int64, device=device)
+        n_h = sum(len(toks) for toks, _, _ in gathered)
+        NSo = max(len(out_names), 1)
+        sc_host = torch.zeros(n_h, 1 + NSo, dtype=torch.float32)
+        r = 0
+        for toks, score, scores in gathered:
+            for e in range(len(toks)):
+                sc_host[r, 0] = float(score[e])
+                for j in range(len(out_names)):
+                    sc_host[r, 1 + j] = float(scores[e, j])
+                r += 1
+        sc_dev = sc_host.to(device)
+        off, r = 0, 0
         for b in range(B):
-            toks, score, scores = eng.gather_ended(b)
-            hyps = [
-                Hypothesis(
-                    yseq=torch.tensor(t, dtype=torch.int64, device=device),
-                    score=torch.tensor(float(score[e]), dtype=torch.float32, device=device),
-                    scores={k: torch.tensor(float(scores[e, j]), device=device) for j, k in enumerate(out_names)},
+            toks, score, scores = gathered[b]
+            hyps, keys = [], []
+            for e, t in enumerate(toks):
+                hyps.append(Hypothesis(
+                    yseq=tok_dev[off : off + len(t)],
+                    score=sc_dev[r, 0],
+                    scores={k: sc_dev[r, 1 + j] for j, k in enumerate(out_names)},
                     states={},
-                )
-                for e, t in enumerate(toks)
-            ]
-            if self.normalize_length:  # beam_search.py:452-459 (python's sort is stable)
-                hyps = sorted(hyps, key=lambda h: float(h.score) / (len(h.yseq) - 1), reverse=True)
-            else:
-                hyps = sorted(hyps, key=lambda h: float(h.score), reverse=True)
+                ))
+                # sort keys from the host copy (no device read per hypothesis): python floats of the fp32 score,
+                # / (len(yseq) - 1) when normalising (beam_search.py:452-459)
+                sc = float(score[e])
+                keys.append(sc / (len(t) - 1) if self.normalize_length else sc)
+                off += len(t)
+                r += 1
+            order = sorted(range(len(hyps)), key=lambda i: keys[i], reverse=True)  # python's sort is stable
+            hyps = [hyps[i] for i in order]
             if len(hyps) == 0:  # retry with a smaller minlenratio, beam_search.py:462-471
                 if minlenratio >= 0.1:
                     hyps = self.decode_batch([xs[b]], maxlenratio, max(0.0, minlenratio - 0.1))[0]

@@ -47,6 +47,7 @@ struct lgasr_handle {
   lgasr_config cfg;
   Dev d;
   int pp, rp, step, begun, have_post;
+  int refilled;  // lgasr_refill was used since lgasr_begin: the utterances are at different decode positions
   int NL;
   size_t smem_rows, smem_sel;
   StepLaunch sl;     // k_step launch geometry
@@ -629,12 +630,46 @@ extern "C" int lgasr_begin(lgasr_handle* h, const int32_t* h_maxlen, const int32
     LAUNCH_CK();
   }
   CK(cudaMemsetAsync(d.status, 0, sizeof(int), st));
-  k_begin<<<d.B, 128, 0, st>>>(d, h->d_primer, h->cfg.primer_len);
+  k_begin<<<d.B, 128, 0, st>>>(d, h->d_primer, h->cfg.primer_len, 0);
   LAUNCH_CK();
   h->pp = 0;
   h->rp = 0;
   h->step = 0;
   h->begun = 1;
+  h->refilled = 0;
+  h->cache_valid = false;
+  return LGASR_OK;
+}
+
+extern "C" int lgasr_refill(lgasr_handle* h, int utt, const float* d_logp, int xlen, int maxlen, int minlen, void* stream) {
+  if (!h) return fail(LGASR_EINVAL, "null handle");
+  if (!h->begun) return fail(LGASR_ESTATE, "lgasr_refill before lgasr_begin");
+  Dev& d = h->d;
+  if (utt < 0 || utt >= d.B) return fail(LGASR_EINVAL, "utt %d out of range", utt);
+  if (xlen < 1 || xlen > d.T) return fail(LGASR_EINVAL, "xlen %d outside [1,%d]", xlen, d.T);
+  if (maxlen > d.maxlen_cap) return fail(LGASR_EINVAL, "maxlen %d > cap %d", maxlen, d.maxlen_cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  h->xlens[utt] = xlen;
+  k_set_utt<<<1, 1, 0, st>>>(d, utt, xlen, maxlen, minlen);
+  LAUNCH_CK();
+  if (d.use_ctc) {
+    if (!d_logp) return fail(LGASR_EINVAL, "null posteriors");
+    float* xT_u = const_cast<float*>(d.xT) + (size_t)utt * d.V * d.Tp;
+    dim3 grid((d.V + 63) / 64, (d.Tp + 63) / 64, 1), block(32, 8);
+    k_transpose_pad<<<grid, block, 0, st>>>(d_logp, xT_u, nullptr, d.T, d.Tp, d.V, d.blank, xlen);
+    LAUNCH_CK();
+    const long long n = (long long)d.W * 2 * d.Tp;
+    for (int p = 0; p < 2; ++p) {
+      k_fill<<<8, 256, 0, st>>>(d.r[p] + (size_t)utt * n, n, LGASR_LOGZERO);
+      LAUNCH_CK();
+    }
+    // the initial state goes where the next position reads its parents
+    k_ctc_init_state<<<1, 128, d.Tp * sizeof(float), st>>>(xT_u, d.r[h->rp] + (size_t)utt * n, d.T, d.Tp, 0, d.W, d.blank, d.W);
+    LAUNCH_CK();
+  }
+  k_begin<<<1, 128, 0, st>>>(d, h->d_primer, h->cfg.primer_len, utt);
+  LAUNCH_CK();
+  h->refilled = 1;
   h->cache_valid = false;
   return LGASR_OK;
 }
@@ -664,7 +699,8 @@ static int fill_terms(lgasr_handle* h, Terms& tm, const float* const* ptr, const
 
 static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl = false, bool flags = false) {
   Dev& d = h->d;
-  if (h->step >= d.maxlen_cap) return fail(LGASR_ESTATE, "step %d beyond max_len_cap %d", h->step, d.maxlen_cap);
+  if (!h->refilled && h->step >= d.maxlen_cap)
+    return fail(LGASR_ESTATE, "step %d beyond max_len_cap %d", h->step, d.maxlen_cap);
   dim3 grid(d.W, d.B);
   cudaEvent_t pe[3] = {nullptr, nullptr, nullptr};
   if (h->profiling) {
@@ -921,7 +957,7 @@ static int refresh_cache(lgasr_handle* h, cudaStream_t st) {
   int mx = 0;
   for (int b = 0; b < d.B; ++b) mx = h->c_n_ended[b] > mx ? h->c_n_ended[b] : mx;
   const int NS = d.NS > 0 ? d.NS : 1;
-  const int steps = h->step;
+  const int steps = (h->refilled || h->step > d.maxlen_cap) ? d.maxlen_cap : h->step;  // trellis rows in use
   h->cache_max_n = mx;
   h->cache_steps = steps;
   h->c_score.resize((size_t)d.B * (mx ? mx : 1));

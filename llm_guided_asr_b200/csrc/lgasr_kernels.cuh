@@ -735,7 +735,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select(Dev d, Terms tm, int pp,
     if (threadIdx.x == 0) utt_carry_done(d, b, pp);
     return;
   }
-  utt_select<false>(d, tm, b, pp, step, smem, d.n_run[pp][b], d.cur_len[pp][b], d.maxlen[b], d.minlen[b]);
+  utt_select<false>(d, tm, b, pp, d.cur_len[pp][b] - d.P, smem, d.n_run[pp][b], d.cur_len[pp][b], d.maxlen[b], d.minlen[b]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -808,8 +808,15 @@ __global__ void k_ctc_init_state(const float* __restrict__ xT, float* __restrict
   }
 }
 
-__global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_len) {
-  const int b = blockIdx.x;
+// lengths of one utterance slot (lgasr_refill): what lgasr_set_posteriors / lgasr_begin copy for a whole batch
+__global__ void k_set_utt(Dev d, int utt, int xlen, int maxlen, int minlen) {
+  const_cast<int*>(d.xlen)[utt] = xlen;
+  const_cast<int*>(d.maxlen)[utt] = maxlen;
+  const_cast<int*>(d.minlen)[utt] = minlen;
+}
+
+__global__ void k_begin(Dev d, const long long* __restrict__ primer, int primer_len, int b0) {
+  const int b = b0 + blockIdx.x;
   const int tid = threadIdx.x;
   const int W = d.W;
   if (tid == 0) {

@@ -727,6 +727,8 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
   const int olen = cur_len - 1;
   const int last = rm.y;
   const int has_parent = rm.x >= 0;
+  // decode position of THIS utterance (the utterances of a handle need not be at the same position: slot refill)
+  const int stepu = cur_len - d.P;
 
   // the two issuing threads initialise their own mbarriers and start their TMA copies before the CTA barrier
   if (tid == 0) {
@@ -756,7 +758,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     if (d.use_ctc) {
       mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
       LGASR_TR(0, 1);
-      group_ctc_scans<NCW>(bR1, bA, bB, bC, bD, has_parent, step == 1, last == rm.z, olen - 1, T, tid, S->ws, kBarCtc,
+      group_ctc_scans<NCW>(bR1, bA, bB, bC, bD, has_parent, stepu == 1, last == rm.z, olen - 1, T, tid, S->ws, kBarCtc,
                            TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
       LGASR_TR(0, 2);
     }
@@ -911,7 +913,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     LGASR_GT(15);
     if (h != 0) return;
     cluster_wait();
-    utt_select<true>(d, tm, b, pp, step, selbuf, n_run, cur_len, maxlen_b, minlen_b,
+    utt_select<true>(d, tm, b, pp, stepu, selbuf, n_run, cur_len, maxlen_b, minlen_b,
                      TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
   } else {
     __syncthreads();
@@ -929,7 +931,7 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     LGASR_TR(0, 6);
     LGASR_GT(15);
     if (!S->last_flag) return;
-    utt_select<false>(d, tm, b, pp, step, arena, n_run, cur_len, maxlen_b, minlen_b,
+    utt_select<false>(d, tm, b, pp, stepu, arena, n_run, cur_len, maxlen_b, minlen_b,
                       TR ? d.trace + ((long long)(blockIdx.y * d.W + blockIdx.x) * 2) * 16 : nullptr);
   }
   LGASR_TR(0, 7);

@@ -232,11 +232,12 @@ class DeviceCachedDecoderScorer(_DeviceCachedScorer):
     """
 
     def __init__(self, decoder: torch.nn.Module, fused_log_softmax: bool = True, cuda_graphs: bool = False,
-                 fused_normaliser: bool = False):
+                 fused_normaliser: bool = False, memory_kv: bool = True):
         for name in ("embed", "decoders", "output_layer"):
             if not hasattr(decoder, name):
                 raise TypeError(f"decoder has no attribute {name!r}: not a BaseTransformerDecoder-like module")
         super().__init__(decoder, fused_log_softmax, cuda_graphs, fused_normaliser)
+        self.memory_kv = memory_kv
 
     @property
     def decoder(self):
@@ -245,17 +246,95 @@ class DeviceCachedDecoderScorer(_DeviceCachedScorer):
     def _n_layers(self) -> int:
         return len(self.net.decoders)
 
+    @staticmethod
+    def _is_reference_layer(layer) -> bool:
+        """The reference's ``DecoderLayer`` (``espnet/nets/pytorch_backend/transformer/decoder_layer.py``): self-attention,
+        source attention, feed-forward, three layer norms, no ``concat_after`` / sequential attention."""
+        att = getattr(layer, "src_attn", None)
+        return (all(hasattr(layer, n) for n in ("self_attn", "src_attn", "feed_forward", "norm1", "norm2", "norm3"))
+                and all(hasattr(att, n) for n in ("linear_q", "linear_k", "linear_v", "linear_out", "h", "d_k"))
+                and not getattr(layer, "concat_after", False) and getattr(layer, "sequential_attn", None) is None)
+
     def _begin_inputs(self, xs, lens, B, W, T, dev, fresh_shape):
-        if fresh_shape:
+        layers = list(self.net.decoders)
+        # memory_kv: the source-attention keys / values of the encoder memory are projected ONCE per utterance and layer
+        # (B x T rows) instead of once per hypothesis row, layer and position (B*beam x T rows, 64 times): the reference
+        # layer re-projects the memory inside every call (attention.py forward_qkv), which is ~99 % of its arithmetic
+        self._fast = self.memory_kv and all(self._is_reference_layer(l) for l in layers)
+        self._BW = (B, W)
+        ar = torch.arange(T, device=dev)
+        mask = ar[None, :] < torch.as_tensor(list(lens), device=dev)[:, None]  # (B, T)
+        if self._fast:
+            mem = xs[0].new_zeros(B, T, xs[0].shape[-1])
+            for b, x in enumerate(xs):
+                mem[b, : lens[b]] = x
+            if fresh_shape or getattr(self, "_mem_kv", None) is None:
+                # static buffers: the CUDA graphs captured for this shape keep reading them in later batches
+                self._mem_kv = [(mem.new_empty(B, l.src_attn.h, l.src_attn.d_k, T), mem.new_empty(B, l.src_attn.h, T, l.src_attn.d_k))
+                                for l in layers]
+                self._mem_pad = torch.zeros(B, 1, 1, T, dtype=torch.bool, device=dev)
+            for l, (kT, v) in zip(layers, self._mem_kv):
+                att = l.src_attn
+                kT.copy_(att.linear_k(mem).view(B, T, att.h, att.d_k).permute(0, 2, 3, 1))  # K stored transposed: (B, H, dk, T)
+                v.copy_(att.linear_v(mem).view(B, T, att.h, att.d_k).transpose(1, 2))
+            self._mem_pad.copy_(~mask[:, None, None, :])  # True on padding frames
+            return
+        if fresh_shape or getattr(self, "_memory", None) is None:
             self._memory = xs[0].new_zeros(B * W, T, xs[0].shape[-1])
             self._memory_mask = torch.zeros(B * W, 1, T, dtype=torch.bool, device=dev)
         mem = self._memory.view(B, W, T, -1)
         mem.zero_()
         for b, x in enumerate(xs):
             mem[b, :, : lens[b]] = x
-        ar = torch.arange(T, device=dev)
-        mask = ar[None, :] < torch.as_tensor(list(lens), device=dev)[:, None]  # (B, T)
         self._memory_mask.view(B, W, T).copy_(mask[:, None, :].expand(B, W, T))
+
+    def _layer_fast(self, layer, x, cache, kT, v, tgt_mask):
+        """One reference ``DecoderLayer`` (``decoder_layer.py:73-150``), same arithmetic per row, with two caches the
+        reference does not keep: the memory keys / values of the utterance (``kT``, ``v``; shared by its ``beam`` rows)
+        and the layer's own self-attention keys / values of the earlier positions (``cache (n, L-1, 2D)``; the reference
+        caches the layer OUTPUTS and re-projects every earlier position at every step, ``attention.py`` forward_qkv).
+        ``x``: the layer input, all positions ``(n, L, D)`` without a cache, the last position ``(n, 1, D)`` with one.
+        Returns ``(output (n, Lq, D), new cache (n, L, 2D))``."""
+        B, W = self._BW
+        nb = layer.normalize_before
+        sa = layer.self_attn
+        n, Lq, D = x.shape
+        H, dk = sa.h, sa.d_k
+        residual = x
+        t = layer.norm1(x) if nb else x
+        kv_new = torch.cat([sa.linear_k(t), sa.linear_v(t)], dim=-1)  # (n, Lq, 2D)
+        kv = kv_new if cache is None else torch.cat([cache, kv_new], dim=1)
+        L = kv.shape[1]
+        q = sa.linear_q(t).view(n, Lq, H, dk).transpose(1, 2)
+        k = kv[..., :D].reshape(n, L, H, dk).transpose(1, 2)
+        vv = kv[..., D:].reshape(n, L, H, dk).transpose(1, 2)
+        scores = torch.matmul(q, k.transpose(-1, -2)) / (dk ** 0.5)  # (n, H, Lq, L)
+        if cache is None and Lq > 1:  # all positions at once: causal mask (the last position alone attends everything)
+            m = ~tgt_mask.unsqueeze(1)
+            scores = scores.masked_fill(m, torch.finfo(scores.dtype).min)
+            p = torch.softmax(scores, dim=-1).masked_fill(m, 0.0)
+        else:
+            p = torch.softmax(scores, dim=-1)
+        h = residual + sa.linear_out(torch.matmul(p, vv).transpose(1, 2).reshape(n, Lq, D))
+        if not nb:
+            h = layer.norm1(h)
+        residual = h
+        y = layer.norm2(h) if nb else h
+        att = layer.src_attn
+        q = att.linear_q(y).view(B, W * Lq, att.h, att.d_k).transpose(1, 2)  # (B, H, W*Lq, dk)
+        scores = torch.matmul(q, kT) / (att.d_k ** 0.5)  # (B, H, W*Lq, T)
+        scores = scores.masked_fill(self._mem_pad, torch.finfo(scores.dtype).min)
+        p = torch.softmax(scores, dim=-1).masked_fill(self._mem_pad, 0.0)
+        ctx = torch.matmul(p, v).transpose(1, 2).reshape(n, Lq, D)  # (B, W*Lq, H, dk) -> rows
+        h = residual + att.linear_out(ctx)
+        if not nb:
+            h = layer.norm2(h)
+        residual = h
+        y = layer.norm3(h) if nb else h
+        h = residual + layer.feed_forward(y)
+        if not nb:
+            h = layer.norm3(h)
+        return h, kv
 
     def _net(self, tgt, cache):
         # the body of forward_one_step (transformer_decoder.py:195-212) without its log_softmax
@@ -263,11 +342,18 @@ class DeviceCachedDecoderScorer(_DeviceCachedScorer):
         L = tgt.shape[1]
         tgt_mask = torch.ones(L, L, dtype=torch.bool, device=tgt.device).tril().unsqueeze(0)
         x = dec.embed(tgt)
-        memory, memory_mask = self._memory, self._memory_mask
         new = []
-        for c, layer in zip(cache, dec.decoders):
-            x, tgt_mask, memory, memory_mask = layer(x, tgt_mask, memory, memory_mask, cache=c)
-            new.append(x)
+        if self._fast:
+            if cache[0] is not None:
+                x = x[:, -1:]  # earlier positions live in the key / value caches
+            for c, layer, (kT, v) in zip(cache, dec.decoders, self._mem_kv):
+                x, kv = self._layer_fast(layer, x, c, kT, v, tgt_mask)
+                new.append(kv)
+        else:
+            memory, memory_mask = self._memory, self._memory_mask
+            for c, layer in zip(cache, dec.decoders):
+                x, tgt_mask, memory, memory_mask = layer(x, tgt_mask, memory, memory_mask, cache=c)
+                new.append(x)
         y = x[:, -1]
         if getattr(dec, "normalize_before", False) and getattr(dec, "after_norm", None) is not None:
             y = dec.after_norm(y)

@@ -115,6 +115,17 @@ class FusedStepEngine:
                 )
             )
 
+    def refill(self, utt: int, logp: Optional[torch.Tensor], xlen: int, maxlen: int, minlen: int):
+        """Continuous batching (``lgasr_refill``): slot ``utt``, whose utterance has finished, takes a new one.
+        ``logp (T, V)`` fp32 log-posteriors of the new utterance on this device (``T`` = the handle's ``max_frames``;
+        frames past ``xlen`` are never read)."""
+        with torch.cuda.device(self.device):
+            if logp is not None:
+                assert logp.is_cuda and logp.dtype == torch.float32 and logp.is_contiguous()
+                assert tuple(logp.shape) == (self.T, self.V), (tuple(logp.shape), (self.T, self.V))
+            _lib.check(self.lib.lgasr_refill(self._h, int(utt), None if logp is None else logp.data_ptr(), int(xlen), int(maxlen),
+                                             int(minlen), _stream_ptr(self.device)))
+
     def _terms(self, mats, consts, weights):
         ptrs, dts, ld = [], [], None
         for m in mats:

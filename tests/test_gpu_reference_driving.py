@@ -131,3 +131,53 @@ def test_reference_batch_beam_search_drives_cuda_scorer(name):
     for h, (toks, score) in zip(nbest, ref):
         assert h.yseq.tolist() == toks
         assert abs(float(h.score) - score) <= SCORE_ATOL
+
+
+@pytest.mark.skipif(not _have_ref(), reason="baseline/_ref not installed (scripts/install_ref.sh)")
+@pytest.mark.parametrize("graphs", [False, True])
+def test_reference_transformer_decoder_under_device_protocol(graphs):
+    """The reference's own TransformerDecoder (random-init) as the full scorer of this package's search: its plain
+    batch_score protocol (per-hypothesis state lists, one utterance at a time) against DeviceCachedDecoderScorer (all row
+    slots of all utterances in one call, memory keys / values per utterance, self-attention key / value caches re-ordered
+    on the device, optional CUDA graphs).  Same n-best lists."""
+    from espnet2.asr.decoder.transformer_decoder import TransformerDecoder
+
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer, LengthBonus
+    from llm_guided_asr_b200.device_cache import DeviceCachedDecoderScorer
+
+    V, D, beam = 150, 32, 4
+    eos = V - 1
+    torch.manual_seed(0)
+    dec = TransformerDecoder(V, D, attention_heads=4, linear_units=64, num_blocks=3, dropout_rate=0.0, positional_dropout_rate=0.0,
+                             self_attention_dropout_rate=0.0, src_attention_dropout_rate=0.0).to(DEV).eval()
+
+    class ProjCTC(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            torch.manual_seed(2)
+            self.lo = torch.nn.Linear(D, V)
+
+        def log_softmax(self, hs):
+            return torch.log_softmax(self.lo(hs), dim=-1)
+
+    ctc = ProjCTC().to(DEV).eval()
+    g = torch.Generator().manual_seed(4)
+    xs = [torch.randn(T, D, generator=g).to(DEV) for T in (33, 27, 33)]
+    weights = dict(decoder=0.7, ctc=0.3, length_bonus=0.2)
+
+    def run(scorer, batch):
+        bs = BatchBeamSearch(scorers=dict(decoder=scorer, ctc=CTCPrefixScorer(ctc=ctc, eos=eos), length_bonus=LengthBonus(V)),
+                             weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
+        with torch.no_grad():
+            return bs.decode_batch(batch, -10, 0.0)
+
+    plain = [run(dec, [x])[0] for x in xs]
+    wrapped = DeviceCachedDecoderScorer(dec, cuda_graphs=graphs)
+    for rep in range(2):  # the second batch replays the captured graphs
+        both = run(wrapped, xs)
+        assert wrapped._fast
+        for p, q in zip(plain, both):
+            assert len(p) == len(q) >= 1
+            for x, y in zip(p, q):
+                assert x.yseq.tolist() == y.yseq.tolist()
+                assert abs(float(x.score) - float(y.score)) <= SCORE_ATOL

@@ -30,9 +30,9 @@ def test_decoder_body_matches_forward_one_step():
     dec = TransformerDecoder(V, D, attention_heads=4, linear_units=64, num_blocks=2, dropout_rate=0.0,
                              positional_dropout_rate=0.0, self_attention_dropout_rate=0.0,
                              src_attention_dropout_rate=0.0).eval()
-    w = DeviceCachedDecoderScorer(dec)
+    w = DeviceCachedDecoderScorer(dec, memory_kv=False)
     memory = torch.randn(n, T, D)
-    w._memory, w._memory_mask = memory, torch.ones(n, 1, T, dtype=torch.bool)
+    w._memory, w._memory_mask, w._fast = memory, torch.ones(n, 1, T, dtype=torch.bool), False
     ys = torch.randint(1, V, (n, 4))
     with torch.no_grad():
         cache = [None] * 2
@@ -45,6 +45,41 @@ def test_decoder_body_matches_forward_one_step():
             for a, b in zip(new, want_cache):
                 assert torch.allclose(a, b, atol=1e-5)
             cache = new
+
+
+def test_decoder_memory_kv_path_matches_forward_one_step():
+    """memory_kv: source-attention keys / values projected once per utterance; rows of two utterances of different
+    lengths against the reference's forward_one_step on the padded, masked memory."""
+    torch.manual_seed(3)
+    V, D, B, W, T = 50, 32, 2, 3, 11
+    lens = [11, 8]
+    dec = TransformerDecoder(V, D, attention_heads=4, linear_units=64, num_blocks=2, dropout_rate=0.0,
+                             positional_dropout_rate=0.0, self_attention_dropout_rate=0.0,
+                             src_attention_dropout_rate=0.0).eval()
+    xs = [torch.randn(t, D) for t in lens]
+    w = DeviceCachedDecoderScorer(dec)
+    n = B * W
+    memory = torch.zeros(n, T, D)
+    mmask = torch.zeros(n, 1, T, dtype=torch.bool)
+    for b in range(B):
+        memory[b * W : (b + 1) * W, : lens[b]] = xs[b]
+        mmask[b * W : (b + 1) * W, :, : lens[b]] = True
+    ys = torch.randint(1, V, (n, 4))
+    with torch.no_grad():
+        w._begin_inputs(xs, lens, B, W, T, torch.device("cpu"), True)
+        assert w._fast
+        cache, ref_cache = [None] * 2, None
+        for L in range(1, 5):
+            tgt = ys[:, :L]
+            mask = torch.ones(L, L, dtype=torch.bool).tril().unsqueeze(0)
+            want, ref_cache = dec.forward_one_step(tgt, mask, memory, mmask, cache=ref_cache)
+            logits, cache = w._net(tgt, cache)  # the fast path caches self-attention keys / values, not layer outputs
+            assert torch.allclose(torch.log_softmax(logits, dim=-1), want, atol=1e-5)
+            assert cache[0].shape == (n, L, 2 * D)
+        # a fresh batch that starts from a longer prefix (no cache yet): all positions are computed
+        logits, new = w._net(ys, [None] * 2)
+        want, _ = dec.forward_one_step(ys, torch.ones(4, 4, dtype=torch.bool).tril().unsqueeze(0), memory, mmask, cache=None)
+        assert torch.allclose(torch.log_softmax(logits, dim=-1), want, atol=1e-5)
 
 
 def test_lm_body_matches_batch_score():
