@@ -190,6 +190,18 @@ int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blank, int m, c
                            const int32_t* d_last, const int32_t* d_sel_hyp, const int32_t* d_sel_tok, int olen,
                            float* d_r_new, void* stream);
 
+/* The same two entry points with the attention window of CTCPrefixScoreTH (margin > 0 with att_w,
+ * ctc_prefix_score.py:56-61,143-148; the ESPnet1 decoders pass attention weights, rnn/decoders.py:665,824-826): the
+ * recursion and the prefix sum run over frames [win_start, win_end) only; (0, 0) = no window.  The caller derives the
+ * window from the attention weights exactly as :143-148 does (CTCPrefixScorer.batch_score_partial(..., att_w=...)). */
+int lgasr_ctc_prefix_score_win(const float* d_xT, int T, int Tp, int V, int blank, int eos, int n, const float* d_r_prev,
+                               const float* d_s_prev, const int32_t* d_last, int olen, const int64_t* d_ids, int S,
+                               float* d_scores, float* d_log_psi, int win_start, int win_end, void* stream);
+int lgasr_ctc_select_state_win(const float* d_xT, int T, int Tp, int blank, int m, const float* d_r_prev,
+                               const int32_t* d_last, const int32_t* d_sel_hyp, const int32_t* d_sel_tok, int olen,
+                               float* d_r_new, int win_start, int win_end, void* stream);
+
+
 /* Streaming extension = CTCPrefixScoreTH.extend_state (ctc_prefix_score.py:246-269) for n survivor states:
  * d_r_old [n][2][Tp_old] valid for T_old frames -> d_r_new [n][2][Tp_new] valid for T_new >= T_old frames of the
  * (extended) posteriors d_xT [V][Tp_new]: old frames copied, new frames r^n = log-zero and

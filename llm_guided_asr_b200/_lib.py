@@ -66,6 +66,8 @@ PROTOTYPES = {
     "lgasr_transpose_posteriors": (_I, [_P, _I, _I, _I, _I, _P, _I, _P]),
     "lgasr_ctc_initial_state": (_I, [_P, _I, _I, _I, _P, _P]),
     "lgasr_ctc_prefix_score": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P, _I, _P, _P, _P]),
+    "lgasr_ctc_prefix_score_win": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P, _I, _P, _P, _I, _I, _P]),
+    "lgasr_ctc_select_state_win": (_I, [_P, _I, _I, _I, _I, _P, _P, _P, _P, _I, _P, _I, _I, _P]),
     "lgasr_ctc_extend_state": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "lgasr_ctc_select_state": (_I, [_P, _I, _I, _I, _I, _P, _P, _P, _P, _I, _P, _P]),
     "lgasr_reorder_rows": (_I, [_P, _P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _P]),

@@ -1237,6 +1237,15 @@ extern "C" int lgasr_ctc_initial_state(const float* d_xT, int T, int Tp, int bla
 extern "C" int lgasr_ctc_prefix_score(const float* d_xT, int T, int Tp, int V, int blank, int eos, int n,
                                       const float* d_r_prev, const float* d_s_prev, const int32_t* d_last, int olen,
                                       const int64_t* d_ids, int S, float* d_scores, float* d_log_psi, void* stream) {
+  return lgasr_ctc_prefix_score_win(d_xT, T, Tp, V, blank, eos, n, d_r_prev, d_s_prev, d_last, olen, d_ids, S, d_scores, d_log_psi,
+                                    0, 0, stream);
+}
+
+extern "C" int lgasr_ctc_prefix_score_win(const float* d_xT, int T, int Tp, int V, int blank, int eos, int n,
+                                          const float* d_r_prev, const float* d_s_prev, const int32_t* d_last, int olen,
+                                          const int64_t* d_ids, int S, float* d_scores, float* d_log_psi, int win_start,
+                                          int win_end, void* stream) {
+  if (win_start < 0 || win_end < 0 || (win_end > 0 && win_start >= win_end) || win_end > T) return fail(LGASR_EINVAL, "bad window");
   if (!d_xT || !d_r_prev || !d_last || !d_scores || !d_log_psi || n < 1 || T < 1 || Tp < T)
     return fail(LGASR_EINVAL, "bad argument");
   if (S > 0 && !d_ids) return fail(LGASR_EINVAL, "null ids");
@@ -1256,7 +1265,8 @@ extern "C" int lgasr_ctc_prefix_score(const float* d_xT, int T, int Tp, int V, i
     }
   }
   k_ctc_prefix_score<<<n, 256, smem, (cudaStream_t)stream>>>(d_xT, T, Tp, V, blank, eos, d_r_prev, d_s_prev, d_last, olen,
-                                                            reinterpret_cast<const long long*>(d_ids), S, d_scores, d_log_psi);
+                                                            reinterpret_cast<const long long*>(d_ids), S, d_scores, d_log_psi,
+                                                            win_start, win_end);
   LAUNCH_CK();
   return LGASR_OK;
 }
@@ -1264,6 +1274,13 @@ extern "C" int lgasr_ctc_prefix_score(const float* d_xT, int T, int Tp, int V, i
 extern "C" int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blank, int m, const float* d_r_prev,
                                       const int32_t* d_last, const int32_t* d_sel_hyp, const int32_t* d_sel_tok, int olen,
                                       float* d_r_new, void* stream) {
+  return lgasr_ctc_select_state_win(d_xT, T, Tp, blank, m, d_r_prev, d_last, d_sel_hyp, d_sel_tok, olen, d_r_new, 0, 0, stream);
+}
+
+extern "C" int lgasr_ctc_select_state_win(const float* d_xT, int T, int Tp, int blank, int m, const float* d_r_prev,
+                                          const int32_t* d_last, const int32_t* d_sel_hyp, const int32_t* d_sel_tok, int olen,
+                                          float* d_r_new, int win_start, int win_end, void* stream) {
+  if (win_start < 0 || win_end < 0 || (win_end > 0 && win_start >= win_end) || win_end > T) return fail(LGASR_EINVAL, "bad window");
   if (!d_xT || !d_r_prev || !d_last || !d_sel_hyp || !d_sel_tok || !d_r_new || m < 1 || T < 1 || Tp < T)
     return fail(LGASR_EINVAL, "bad argument");
   const size_t smem = (size_t)4 * Tp * sizeof(float);
@@ -1282,7 +1299,7 @@ extern "C" int lgasr_ctc_select_state(const float* d_xT, int T, int Tp, int blan
     }
   }
   k_ctc_select_state<<<m, 32, smem, (cudaStream_t)stream>>>(d_xT, T, Tp, blank, d_r_prev, d_last, d_sel_hyp, d_sel_tok, olen,
-                                                           d_r_new);
+                                                           d_r_new, win_start, win_end);
   LAUNCH_CK();
   return LGASR_OK;
 }

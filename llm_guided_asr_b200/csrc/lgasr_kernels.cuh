@@ -132,7 +132,12 @@ __device__ __forceinline__ void warp_ctc_state(const float* __restrict__ xT_b,  
                                                const float* __restrict__ r_par,  // [2][Tp] parent state (or own)
                                                float* __restrict__ r_out,        // [2][Tp] own state (written)
                                                int has_parent, int tok, int par_last, int olen_par, int T, int Tp,
-                                               int blank, float* bA, float* bB, float* bC, float* bD, int lane) {
+                                               int blank, float* bA, float* bB, float* bC, float* bD, int lane,
+                                               int win_s = 0, int win_e = 0) {
+  // attention window (ctc_prefix_score.py:143-148): the recursion runs over frames [win_s, win_e) only (0, 0: the whole
+  // utterance from max(output_length, 1)); frames outside keep log-zero
+  const int Tall = T;
+  if (win_e > 0 && win_e < T) T = win_e;
   if (!has_parent) {
     for (int t = lane; t < T; t += 32) {
       float rn = r_par[t], rb = r_par[Tp + t];
@@ -144,7 +149,7 @@ __device__ __forceinline__ void warp_ctc_state(const float* __restrict__ xT_b,  
     __syncwarp();
     return;
   }
-  const int start = olen_par > 1 ? olen_par : 1;
+  const int start = win_s > 0 ? win_s : (olen_par > 1 ? olen_par : 1);
   const float* xc = xT_b + (long long)tok * Tp;
   const float* x0 = xT_b + (long long)blank * Tp;
   const bool same = (tok == par_last);
@@ -156,7 +161,7 @@ __device__ __forceinline__ void warp_ctc_state(const float* __restrict__ xT_b,  
     bC[t] = __ldg(x0 + t);
   }
   __syncwarp();
-  const float rn0 = (olen_par == 0) ? bA[0] : LGASR_LOGZERO;  // r[start-1, 0]  (:128-129)
+  const float rn0 = (olen_par == 0 && start == 1) ? bA[0] : LGASR_LOGZERO;  // r[start-1, 0]  (:128-129)
   for (int t = start + lane; t < T; t += 32) bB[t] = bD[t - 1] + bA[t];
   __syncwarp();
   warp_affine_scan(bA, bB, start, T, rn0, lane);  // bB = r^n
@@ -169,9 +174,12 @@ __device__ __forceinline__ void warp_ctc_state(const float* __restrict__ xT_b,  
   __syncwarp();
   warp_affine_scan(bC, bD, start, T, LGASR_LOGZERO, lane);  // bD = r^b
   __syncwarp();
-  for (int t = lane; t < T; t += 32) {
+  for (int t = lane; t < Tall; t += 32) {
     float rn, rb;
-    if (t >= start) {
+    if (t >= T) {
+      rn = LGASR_LOGZERO;
+      rb = LGASR_LOGZERO;
+    } else if (t >= start) {
       rn = bB[t];
       rb = bD[t];
     } else if (t == start - 1) {

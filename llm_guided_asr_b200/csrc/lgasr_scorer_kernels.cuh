@@ -12,7 +12,8 @@ __global__ void __launch_bounds__(256) k_ctc_prefix_score(const float* __restric
                                                           const float* __restrict__ s_prev_arr,
                                                           const int* __restrict__ last_arr, int olen,
                                                           const long long* __restrict__ ids, int S,
-                                                          float* __restrict__ scores, float* __restrict__ log_psi) {
+                                                          float* __restrict__ scores, float* __restrict__ log_psi,
+                                                          int win_s, int win_e) {
   extern __shared__ float smem[];
   float* phi_sum = smem;
   float* rbv = smem + Tp;
@@ -35,15 +36,17 @@ __global__ void __launch_bounds__(256) k_ctc_prefix_score(const float* __restric
     }
   }
   __syncthreads();
-  const int start = olen > 1 ? olen : 1;
+  // attention window (ctc_prefix_score.py:143-148): the sum runs over frames [win_s, win_e) (0, 0: [max(olen, 1), T))
+  const int start = win_s > 0 ? win_s : (olen > 1 ? olen : 1);
+  const int Tend = (win_e > 0 && win_e < T) ? win_e : T;
   const int ncand = S > 0 ? S : V;
   for (int j = warp; j < ncand; j += blockDim.x / 32) {
     const int c = S > 0 ? (int)ids[(long long)h * S + j] : j;
     if (c < 0 || c >= V) continue;
     const float* phi = (c == last) ? rbv : phi_sum;
     const float* xr = xT + (long long)c * Tp;
-    const float rn0 = (olen == 0) ? __ldg(xr) : LGASR_LOGZERO;
-    const float psi = warp_prefix_lse(phi, xr, start, T, rn0, lane);
+    const float rn0 = (olen == 0 && start == 1) ? __ldg(xr) : LGASR_LOGZERO;  // r[start-1, 0]
+    const float psi = warp_prefix_lse(phi, xr, start, Tend, rn0, lane);
     if (lane == 0) {
       lp[c] = psi;
       sc[c] = __fsub_rn(psi, s_prev);
@@ -67,12 +70,12 @@ __global__ void __launch_bounds__(32) k_ctc_select_state(const float* __restrict
                                                          const int* __restrict__ last_arr,
                                                          const int* __restrict__ sel_hyp,
                                                          const int* __restrict__ sel_tok, int olen,
-                                                         float* __restrict__ r_new) {
+                                                         float* __restrict__ r_new, int win_s, int win_e) {
   extern __shared__ float smem[];
   const int i = blockIdx.x, lane = threadIdx.x;
   const int h = sel_hyp[i], c = sel_tok[i];
   warp_ctc_state(xT, r_prev + (long long)h * 2 * Tp, r_new + (long long)i * 2 * Tp, 1, c, last_arr[h], olen, T, Tp, blank,
-                 smem, smem + Tp, smem + 2 * Tp, smem + 3 * Tp, lane);
+                 smem, smem + Tp, smem + 2 * Tp, smem + 3 * Tp, lane, win_s, win_e);
 }
 
 // CTCPrefixScoreTH.extend_state (ctc_prefix_score.py:246-269): one block per survivor state

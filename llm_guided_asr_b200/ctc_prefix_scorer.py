@@ -14,7 +14,7 @@ Same constructor and methods as the reference class, so an *unmodified* referenc
 The fused search (``llm_guided_asr_b200.beam_search.BatchBeamSearch``) does not call these methods:
 it only takes ``.ctc`` and ``.eos`` from this object and runs the same device functions inside the
 fused step kernels.  ``extend_prob`` / ``extend_state`` are the streaming extension of the scorer API
-(``scorers/ctc.py:128-157``); the per-hypothesis state here is ``(r (2, Tp), s, T)``.
+(``scorers/ctc.py:128-157``); the per-hypothesis state here is ``(r (2, Tp), s, T, (f_min, f_max))``.
 """
 
 import ctypes as C
@@ -35,9 +35,12 @@ def _st(dev):
 class CTCPrefixScorer(BatchPartialScorerInterface):
     """Decoder interface wrapper for the CUDA CTC prefix scorer."""
 
-    def __init__(self, ctc: torch.nn.Module, eos: int):
+    def __init__(self, ctc: torch.nn.Module, eos: int, margin: int = 0):
         self.ctc = ctc
         self.eos = eos
+        # attention-window margin of CTCPrefixScoreTH (ctc_prefix_score.py:21,56-61): with margin > 0 and attention
+        # weights passed to batch_score_partial the recursion is restricted to frames around the attention peak
+        self.margin = int(margin)
         self.blank = 0  # scorers/ctc.py:98
         self.impl = None  # dict with the per-utterance device buffers
 
@@ -56,7 +59,7 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
             _lib.check(lib.lgasr_ctc_initial_state(xT.data_ptr(), T, Tp, self.blank, r0.data_ptr(), _st(x.device)))
         self.impl = dict(lib=lib, xT=xT, r0=r0, T=T, Tp=Tp, V=V, device=x.device, dtype=x.dtype)
 
-    def _score(self, last: torch.Tensor, olen: int, r_prev: torch.Tensor, s_prev: torch.Tensor, ids):
+    def _score(self, last: torch.Tensor, olen: int, r_prev: torch.Tensor, s_prev: torch.Tensor, ids, win=(0, 0)):
         m = self.impl
         n = r_prev.shape[0]
         S = 0 if ids is None else ids.shape[1]
@@ -65,23 +68,24 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         ids64 = None if ids is None else ids.to(torch.int64).contiguous()
         with torch.cuda.device(m["device"]):
             _lib.check(
-                m["lib"].lgasr_ctc_prefix_score(
+                m["lib"].lgasr_ctc_prefix_score_win(
                     m["xT"].data_ptr(), m["T"], m["Tp"], m["V"], self.blank, self.eos, n,
                     r_prev.data_ptr(), s_prev.data_ptr(), last.data_ptr(), olen,
-                    None if ids64 is None else ids64.data_ptr(), S, scores.data_ptr(), log_psi.data_ptr(), _st(m["device"]),
+                    None if ids64 is None else ids64.data_ptr(), S, scores.data_ptr(), log_psi.data_ptr(),
+                    int(win[0]), int(win[1]), _st(m["device"]),
                 )
             )
         return scores, log_psi
 
-    def _select(self, r_prev: torch.Tensor, last: torch.Tensor, hyp: torch.Tensor, tok: torch.Tensor, olen: int):
+    def _select(self, r_prev: torch.Tensor, last: torch.Tensor, hyp: torch.Tensor, tok: torch.Tensor, olen: int, win=(0, 0)):
         m = self.impl
         k = hyp.shape[0]
         r_new = torch.empty(k, 2, m["Tp"], dtype=torch.float32, device=m["device"])
         with torch.cuda.device(m["device"]):
             _lib.check(
-                m["lib"].lgasr_ctc_select_state(
+                m["lib"].lgasr_ctc_select_state_win(
                     m["xT"].data_ptr(), m["T"], m["Tp"], self.blank, k, r_prev.data_ptr(), last.data_ptr(),
-                    hyp.data_ptr(), tok.data_ptr(), olen, r_new.data_ptr(), _st(m["device"]),
+                    hyp.data_ptr(), tok.data_ptr(), olen, r_new.data_ptr(), int(win[0]), int(win[1]), _st(m["device"]),
                 )
             )
         return r_new
@@ -91,36 +95,51 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         self._setup(x)
         return None
 
-    def batch_score_partial(self, y, ids, state, x):
+    def batch_score_partial(self, y, ids, state, x, att_w=None):
         """``y (n, L)`` int64 prefixes, ``ids (n, S)`` int64 candidates or None, ``state`` list of
-        per-hypothesis states (None at the first position).  Returns ``(scores (n, V), batch state)``."""
+        per-hypothesis states (None at the first position).  Returns ``(scores (n, V), batch state)``.
+
+        ``att_w (n, T)`` (optional, with ``margin > 0``): attention weights of the hypotheses; the frame window is
+        derived from them as ``ctc_prefix_score.py:143-148`` does and carried in the state (``f_min``, ``f_max``)."""
         m = self.impl
         n = len(y)
         dev = m["device"]
         olen = len(y[0]) - 1
+        f_prev = (0, 1)  # ctc_prefix_score.py:93-94
         if state is None or state[0] is None:
             r_prev = m["r0"].unsqueeze(0).expand(n, 2, m["Tp"]).contiguous()
             s_prev = torch.zeros(n, dtype=torch.float32, device=dev)
         else:
             r_prev = torch.stack([s[0] for s in state]).contiguous()
             s_prev = torch.stack([s[1] for s in state]).to(torch.float32).contiguous()
+            if len(state[0]) > 3:
+                f_prev = (max(s[3][0] for s in state), max(s[3][1] for s in state))
         if torch.is_tensor(y):  # (n, L) prefixes: the last tokens stay on the device (no per-hypothesis sync)
             last = y[:, -1].to(device=dev, dtype=torch.int32).contiguous()
         else:
             last = torch.as_tensor([int(yi[-1]) for yi in y], dtype=torch.int32, device=dev)
-        scores, log_psi = self._score(last, olen, r_prev, s_prev, ids)
-        return scores.to(m["dtype"]), (r_prev, log_psi, last, olen, "lgasr")
+        win, f_now = (0, 0), (0, 0)
+        if att_w is not None and self.margin > 0:
+            T = m["T"]
+            f_arg = torch.matmul(att_w.to(device=dev, dtype=torch.float32), torch.arange(T, dtype=torch.float32, device=dev))
+            lo_hi = torch.stack([f_arg.min(), f_arg.max()]).cpu()  # one host read, as the reference's .cpu() calls
+            f_min = max(int(lo_hi[0]), f_prev[0])
+            f_max = max(int(lo_hi[1]), f_prev[1])
+            win = (min(f_prev[1], max(f_min - self.margin, olen, 1)), min(f_max + self.margin, T))
+            f_now = (f_min, f_max)
+        scores, log_psi = self._score(last, olen, r_prev, s_prev, ids, win)
+        return scores.to(m["dtype"]), (r_prev, log_psi, last, olen, "lgasr", win, f_now)
 
     def select_state(self, state, i, new_id=None):
         if isinstance(state, list):  # list of per-hypothesis states (batchfy / unbatchfy)
             return state[i]
-        if type(state) is tuple and len(state) == 5 and state[4] == "lgasr":  # batch state of this class
-            r_prev, log_psi, last, olen, _ = state
+        if type(state) is tuple and len(state) == 7 and state[4] == "lgasr":  # batch state of this class
+            r_prev, log_psi, last, olen, _, win, f_now = state
             dev = r_prev.device
             hyp = torch.as_tensor([int(i)], dtype=torch.int32, device=dev)
             tok = torch.as_tensor([int(new_id)], dtype=torch.int32, device=dev)
-            r_new = self._select(r_prev, last, hyp, tok, olen)[0]
-            return r_new, log_psi[int(i), int(new_id)], self.impl["T"]
+            r_new = self._select(r_prev, last, hyp, tok, olen, win)[0]
+            return r_new, log_psi[int(i), int(new_id)], self.impl["T"], f_now
         if type(state) is tuple and len(state) == 2 and torch.is_tensor(state[0]) and state[0].dim() > 0:
             # non-batch API: (scores over the candidate ids, states over the candidate ids)
             sc, st = state
@@ -190,5 +209,5 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
                     )
                 )
             for k, i in enumerate(idx):
-                out[i] = (r_new[k], state[i][1], m["T"])
+                out[i] = (r_new[k], state[i][1], m["T"]) + tuple(state[i][3:])
         return out

@@ -34,7 +34,8 @@ def _lse_axis0(v):
 class CTCPrefixOracle:
     """One utterance: ``logp (T, V)`` fp32 log-posteriors, ``blank``, ``eos``."""
 
-    def __init__(self, logp, blank, eos, xlen=None):
+    def __init__(self, logp, blank, eos, xlen=None, margin=0):
+        self.margin = margin  # attention-window margin (:56-61); 0 = no windowing
         x = np.array(logp, dtype=np.float32, copy=True)
         T, V = x.shape
         # padding rule of ctc_prefix_score.py:46-49
@@ -52,8 +53,12 @@ class CTCPrefixOracle:
         r[:, 1, 0] = np.cumsum(self.x[:, self.blank], dtype=np.float32)
         return r, np.zeros((1,), dtype=np.float32)
 
-    def __call__(self, last_ids, output_length, r_prev, s_prev, ids):
-        """One prefix-extension step (``CTCPrefixScoreTH.__call__`` :67-187, no windowing).
+    def __call__(self, last_ids, output_length, r_prev, s_prev, ids, att_w=None, f_prev=(0, 1)):
+        """One prefix-extension step (``CTCPrefixScoreTH.__call__`` :67-187).
+
+        ``att_w (n, T)`` attention weights and ``f_prev = (f_min, f_max)`` of the previous call select the frame window
+        when ``margin > 0`` (:143-148); ``self.last_window`` then holds ``(start, end, f_min, f_max)``.  The first call
+        starts from ``(f_min, f_max) = (0, 1)`` (:93-94), so ``start >= 1`` always.
 
         last_ids (n,) int; output_length = len(y) - 1; r_prev (T, 2, n); s_prev (n,) prefix
         scores of the hypotheses; ids (n, S) candidate tokens or None (full vocabulary).
@@ -87,7 +92,16 @@ class CTCPrefixOracle:
             else:
                 log_phi[:, h, last_ids[h]] = r_prev[:, 1, h]
 
-        start, end = max(output_length, 1), T  # :150-152
+        if att_w is not None and self.margin > 0:  # :143-148
+            f_arg = np.matmul(np.asarray(att_w, dtype=np.float32), np.arange(T, dtype=np.float32))
+            f_min = max(int(f_arg.min()), f_prev[0])
+            f_max = max(int(f_arg.max()), f_prev[1])
+            start = min(f_prev[1], max(f_min - self.margin, output_length, 1))
+            end = min(f_max + self.margin, T)
+        else:
+            f_min = f_max = 0
+            start, end = max(output_length, 1), T  # :150-152
+        self.last_window = (start, end, f_min, f_max)
         for t in range(start, end):  # :155-160
             rn = _lse2(r[t - 1, 0], log_phi[t - 1]) + xn[t]
             rb = _lse2(r[t - 1, 0], r[t - 1, 1]) + xb[t]

@@ -16,7 +16,7 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GOLDEN_NAMES = sorted(
     os.path.basename(p)[:-4]
     for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz"))
-    if os.path.basename(p) not in ("streaming.npz", "score_filter.npz") and not os.path.basename(p).startswith("nb_")
+    if os.path.basename(p) not in ("streaming.npz", "score_filter.npz", "att_window.npz") and not os.path.basename(p).startswith("nb_")
 )
 # non-batch goldens (make_golden_nonbatch.py): reference BeamSearch + NumPy CTCPrefixScore
 NONBATCH_NAMES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, "nb_*.npz")))
