@@ -381,17 +381,20 @@ def run_configs4(rank, world, dev, cfg, n_utts=4096, batch=512, K=2, reps=2):
     names = ["decoder", "lm"][:K]
     pos = {tuple(idx): bi for bi, idx in enumerate(my_batches)}
 
+    turn = [0]
+
     def decode_fn(idx):
         bi = pos[tuple(idx)]
         Bb = len(idx)
-        eng = engines.get(Bb)
+        turn[0] ^= 1  # two handles per batch size: batch i + 1 decodes while batch i is read back
+        eng = engines.get((Bb, turn[0]))
         if eng is None:
-            eng = engines[Bb] = FusedStepEngine(Bb, T, V, W, cfg["S"], names, "full", True, cfg["ctc_weight"], eos, eos, L, 1,
-                                                False, device=dev)
+            eng = engines[(Bb, turn[0])] = FusedStepEngine(Bb, T, V, W, cfg["S"], names, "full", True, cfg["ctc_weight"], eos, eos,
+                                                           L, 1, False, device=dev)
         eng.set_posteriors(logps[bi], [lengths[i] for i in idx])
         eng.begin([L] * Bb, [0] * Bb, [eos])
         eng.replay([[t[i][: Bb * W] for t in tabs] for i in range(L)], consts, wts, ld=V)
-        return eng.gather_best()
+        return eng.gather_best  # deferred read-back (sharding.decode_sharded calls it after queueing the next batch)
 
     times = []
     merged = None

@@ -48,8 +48,12 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
     def _setup(self, x: torch.Tensor):
         if not x.is_cuda:
             raise RuntimeError("CTCPrefixScorer (sm_100a) needs CUDA tensors: there is no CPU fallback")
+        if x.dtype == torch.float64:
+            # the reference follows x.dtype (ctc_prefix_score.py:38); the kernels are fp32: refuse rather than lose
+            # precision silently
+            raise NotImplementedError("CTCPrefixScorer (sm_100a kernels) computes in fp32: float64 encoder output is not supported")
         lib = _lib.load()
-        logp = self.ctc.log_softmax(x.unsqueeze(0))[0].to(torch.float32).contiguous()
+        logp = self.ctc.log_softmax(x.unsqueeze(0))[0].to(torch.float32).contiguous()  # fp16 / bf16 inputs are widened
         T, V = logp.shape
         Tp = (T + 3) & ~3
         xT = torch.empty(V, Tp, dtype=torch.float32, device=x.device)

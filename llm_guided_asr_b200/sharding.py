@@ -42,16 +42,38 @@ def batches(indices: Sequence[int], lengths: Sequence[int], batch_size: int) -> 
 Record = Tuple[int, List[int], float]  # (utterance index, best token sequence, score)
 
 
-def gather_records(local: List[Record], rank: int, world: int, group=None) -> Optional[List[Record]]:
+def gather_records(local: List[Record], rank: int, world: int, group=None, device=None) -> Optional[List[Record]]:
     """The final hypothesis gather: rank 0 receives every shard's records, sorted by utterance index
-    (the ``cat | sort -k1`` of ``asr.sh:1603-1612``); other ranks return None."""
+    (the ``cat | sort -k1`` of ``asr.sh:1603-1612``); other ranks return None.
+
+    The records travel as ONE padded int32 tensor per rank (index, length, fp32 score bits, tokens) through
+    ``dist.gather`` (NCCL over NVLink when ``device`` is a CUDA device, gloo on the CPU): one small all-reduce for the
+    extents, one gather; no pickling."""
     if world == 1 or not dist.is_initialized():
         return sorted(local, key=lambda r: r[0])
-    out = [None] * world if rank == 0 else None
-    dist.gather_object(local, out, dst=0, group=group)
+    import numpy as np
+
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    ext = torch.tensor([len(local), max((len(r[1]) for r in local), default=0)], dtype=torch.int64, device=device)
+    dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=group)
+    n_max, l_max = int(ext[0]), int(ext[1])
+    pack = np.full((n_max, 3 + l_max), -1, dtype=np.int32)
+    for i, (idx, toks, score) in enumerate(local):
+        pack[i, 0] = idx
+        pack[i, 1] = len(toks)
+        pack[i, 2] = np.float32(score).view(np.int32)
+        pack[i, 3 : 3 + len(toks)] = toks
+    t = torch.from_numpy(pack).to(device)
+    out = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+    dist.gather(t, out, dst=0, group=group)
     if rank != 0:
         return None
-    merged = [r for shard in out for r in shard]
+    merged: List[Record] = []
+    for o in out:
+        a = o.cpu().numpy()
+        for row in a[a[:, 0] >= 0]:
+            merged.append((int(row[0]), [int(v) for v in row[3 : 3 + int(row[1])]], float(row[2:3].view(np.float32)[0])))
     return sorted(merged, key=lambda r: r[0])
 
 
@@ -75,12 +97,28 @@ def decode_sharded(
         world = dist.get_world_size(group) if dist.is_initialized() else 1
     mine = partition(lengths, world)[rank]
     local: List[Record] = []
-    for b in batches(mine, lengths, batch_size):
-        res = decode_fn(b)
+
+    def collect(b, res):
         if len(res) != len(b):
             raise RuntimeError(f"decode_fn returned {len(res)} results for a batch of {len(b)}")
         for i, (toks, score) in zip(b, res):
             local.append((int(i), [int(t) for t in toks], float(score)))
+
+    # decode_fn may return a callable instead of the results: the batch has been QUEUED on the device and the callable
+    # reads it back; it is called after the next batch has been queued, so the read-back of batch i overlaps the decode
+    # of batch i + 1
+    pending = None
+    for b in batches(mine, lengths, batch_size):
+        res = decode_fn(b)
+        if pending is not None:
+            collect(pending[0], pending[1]())
+            pending = None
+        if callable(res):
+            pending = (b, res)
+        else:
+            collect(b, res)
+    if pending is not None:
+        collect(pending[0], pending[1]())
     return gather_records(local, rank, world, group)
 
 
