@@ -215,12 +215,10 @@ __device__ __forceinline__ void group_ctc_scans(const float* bR1, const float* b
 // lay out the shifted phi arrays of the psi phase (see above).  Ends with a CTA barrier.
 __device__ __forceinline__ void cta_ctc_epilogue(float* bR0, float* bR1, const float* bA, float* bB, const float* bC,
                                                  float* bD, float* __restrict__ r_out, int has_parent, int olen_par, int T,
-                                                 int Tp, int tid, float* psi_eos, unsigned (*wm)[kStepWarps], float* M0,
-                                                 float* M1) {
+                                                 int Tp, int tid, float* psi_eos) {
   const int start = olen_par > 1 ? olen_par : 1;
   const int pstart = olen_par + 1 > 1 ? olen_par + 1 : 1;  // max(olen, 1) of this hypothesis
   const float rn0 = (has_parent && olen_par == 0) ? bA[0] : LGASR_LOGZERO;
-  float m0 = LGASR_NEG, m1 = LGASR_NEG;  // maxima of the two phi arrays (the psi phase sums relative to them)
 #pragma unroll 1
   for (int u = tid; u <= Tp; u += kStepThreads) {
     const int t = u - 1;  // state of frame t
@@ -247,31 +245,11 @@ __device__ __forceinline__ void cta_ctc_epilogue(float* bR0, float* bR1, const f
       // !has_parent: bR0/bR1[t] are still read by the thread that owns u = t + 1: stage in bB/bD
       float* o0 = has_parent ? bR0 : bB;
       float* o1 = has_parent ? bR1 : bD;
-      const float v0 = in ? rs : LGASR_NEG, v1 = in ? rb : LGASR_NEG;
-      o0[u] = v0;
-      o1[u] = v1;
-      m0 = fmaxf(m0, v0);
-      m1 = fmaxf(m1, v1);
-    }
-  }
-  {
-    const unsigned q0 = __reduce_max_sync(FULLMASK, f2ord(m0)), q1 = __reduce_max_sync(FULLMASK, f2ord(m1));
-    if ((tid & 31) == 0) {
-      wm[0][tid >> 5] = q0;
-      wm[1][tid >> 5] = q1;
+      o0[u] = in ? rs : LGASR_NEG;
+      o1[u] = in ? rb : LGASR_NEG;
     }
   }
   __syncthreads();
-  {
-    unsigned a = wm[0][0], c = wm[1][0];
-#pragma unroll
-    for (int w2 = 1; w2 < kStepWarps; ++w2) {
-      a = max(a, wm[0][w2]);
-      c = max(c, wm[1][w2]);
-    }
-    *M0 = ord2f(a);
-    *M1 = ord2f(c);
-  }
   if (!has_parent) {
     for (int u = tid; u < Tp; u += kStepThreads) {
       bR0[u] = bB[u];
@@ -293,7 +271,6 @@ struct __align__(16) StepSmem {
   int last_flag, pad0;
   float ws[2 * kStepWarps];
   unsigned wkth[kStepWarps];
-  unsigned wm[2][kStepWarps];               // per-warp maxima of the two phi arrays (ordered integers)
 };
 
 // debug time line: stamp i of group grp (0 ctc / all, 1 sel) of this CTA
@@ -789,10 +766,9 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
     sel_phase();
   }
   __syncthreads();
-  float M0 = LGASR_NEG, M1 = LGASR_NEG;
   if (d.use_ctc)
     cta_ctc_epilogue(bR0, bR1, bA, bB, bC, bD, d.r[rp ^ 1] + ((long long)row * 2) * Tp, has_parent, olen - 1, T, Tp, tid,
-                     &S->psi_eos, S->wm, &M0, &M1);
+                     &S->psi_eos);
   LGASR_TR(0, 3);
 
   // ======================= all warps: candidate records ===============================================
@@ -867,50 +843,32 @@ __global__ void __launch_bounds__(kStepThreads, 5) k_step(Dev d, Terms tm, StepL
         const int jr = g0 + (have ? i : i0);
         const int c = key_idx(tk[jr]);
         const bool special = (c == d.eos) || (d.eos != d.blank && c == d.blank);
-        // log psi = logsumexp({phi[t-1] + x[t] : start <= t < T} U {r^n[start-1]})  (:163-171).  phi is
-        // pre-shifted and LGASR_NEG outside [start, T), so the sum runs over whole float4 rows.  (A special
-        // candidate runs the same code on whatever its arena slot holds and discards the result.)
+        // log psi = logsumexp({phi[t-1] + x[t] : start <= t < T} U {r^n[start-1]})  (:163-171), the way
+        // torch.logsumexp does it (max, sum of exp, log).  phi is pre-shifted and LGASR_NEG outside
+        // [start, T), so the sum runs over whole float4 rows.  (A special candidate runs the same code on
+        // whatever its arena slot holds and discards the result.)
         const float4* x4 = reinterpret_cast<const float4*>(arena + (long long)(jr - g0) * Tp);
-        const bool rp1 = (c == last);
-        const float4* p4 = reinterpret_cast<const float4*>(rp1 ? bR1 : bR0);
+        const float4* p4 = reinterpret_cast<const float4*>((c == last) ? bR1 : bR0);
         const float rn0 = (olen == 0) ? arena[(long long)(jr - g0) * Tp] : LGASR_LOGZERO;
-        // ONE sweep: every term relative to M = max(phi) (x <= 0, so no term exceeds 1); (phi - M) first: that
-        // subtraction is exact near the maximum, where the terms matter
-        const float M = fmaxf(rp1 ? M1 : M0, rn0);
-        float sum = (hl == 0) ? ex2_approx((rn0 - M) * kL2E) : 0.f;
-#pragma unroll 2
+        float m = rn0;
+#pragma unroll 1
         for (int q = hl; q < nq; q += 16) {
           const float4 xa = x4[q], pa = p4[q];
-          sum += ex2_approx(((pa.x - M) + xa.x) * kL2E) + ex2_approx(((pa.y - M) + xa.y) * kL2E) +
-                 ex2_approx(((pa.z - M) + xa.z) * kL2E) + ex2_approx(((pa.w - M) + xa.w) * kL2E);
+          m = fmaxf(fmaxf(fmaxf(m, pa.x + xa.x), fmaxf(pa.y + xa.y, pa.z + xa.z)), pa.w + xa.w);
+        }
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULLMASK, m, o));
+        // (e - m) first: the subtraction is exact near the maximum, where the terms matter
+        float sum = (hl == 0) ? ex2_approx((rn0 - m) * kL2E) : 0.f;
+#pragma unroll 1
+        for (int q = hl; q < nq; q += 16) {
+          const float4 xa = x4[q], pa = p4[q];
+          sum += ex2_approx((pa.x + xa.x - m) * kL2E) + ex2_approx((pa.y + xa.y - m) * kL2E) +
+                 ex2_approx((pa.z + xa.z - m) * kL2E) + ex2_approx((pa.w + xa.w - m) * kL2E);
         }
 #pragma unroll
         for (int o = 8; o >= 1; o >>= 1) sum += __shfl_xor_sync(FULLMASK, sum, o);
-        float psi = M + logf(sum);
-        // a candidate whose every frame lies far below the hypothesis' own mass (or x > 0 somewhere) leaves the fp32
-        // range of the one-sweep sum: the exact two sweeps (max, then sum of exp), as torch.logsumexp does it
-        const bool bad = !special && have && !(sum > 1e-30f && sum < 1e30f);
-        if (__any_sync(FULLMASK, bad)) {
-          float m = rn0;
-#pragma unroll 1
-          for (int q = hl; q < nq; q += 16) {
-            const float4 xa = x4[q], pa = p4[q];
-            m = fmaxf(fmaxf(fmaxf(m, pa.x + xa.x), fmaxf(pa.y + xa.y, pa.z + xa.z)), pa.w + xa.w);
-          }
-#pragma unroll
-          for (int o = 8; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULLMASK, m, o));
-          // (e - m) first: the subtraction is exact near the maximum, where the terms matter
-          float s2 = (hl == 0) ? ex2_approx((rn0 - m) * kL2E) : 0.f;
-#pragma unroll 1
-          for (int q = hl; q < nq; q += 16) {
-            const float4 xa = x4[q], pa = p4[q];
-            s2 += ex2_approx((pa.x + xa.x - m) * kL2E) + ex2_approx((pa.y + xa.y - m) * kL2E) +
-                  ex2_approx((pa.z + xa.z - m) * kL2E) + ex2_approx((pa.w + xa.w - m) * kL2E);
-          }
-#pragma unroll
-          for (int o = 8; o >= 1; o >>= 1) s2 += __shfl_xor_sync(FULLMASK, s2, o);
-          if (bad) psi = m + logf(s2);
-        }
+        float psi = m + logf(sum);
         if (c == d.eos)
           psi = psi_eos;
         else if (special)
