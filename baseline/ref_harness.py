@@ -97,25 +97,51 @@ def decode_one(logp_b, tables_b, cfg, positions, device="cpu", lm_tables_b=None,
     return dt, [([int(t) for t in h.yseq.tolist()], float(h.score)) for h in nb]
 
 
-def _worker(args):
+_SHARED = {}
+
+
+def _worker(b):
+    """One utterance in a pool worker.  The inputs are inherited through fork (``_SHARED``), only the index travels."""
     import torch
 
     torch.set_num_threads(1)
-    logp_b, tables_b, cfg, positions = args
-    return decode_one(torch.from_numpy(logp_b), torch.from_numpy(tables_b), cfg, positions)
+    sh = _SHARED
+    W = sh["cfg"]["beam"]
+    L = sh["positions"]
+    return decode_one(sh["logp"][b], sh["tables"][:L, b * W : (b + 1) * W], sh["cfg"], L)
+
+
+class CpuPool:
+    """``procs`` single-threaded reference processes (job-level sharding as ``egs2/*/asr.sh`` ``inference_nj``), forked
+    once with the inputs in their address space; ``run(utts)`` decodes the utterances and returns (wall seconds of the
+    decodes only - no process start-up, no input pickling -, results)."""
+
+    def __init__(self, logp, tables, cfg, positions, procs):
+        import multiprocessing as mp
+
+        _SHARED.update(logp=logp, tables=tables, cfg=cfg, positions=positions)
+        self.procs = procs
+        self.pool = mp.get_context("fork").Pool(procs) if procs > 1 else None
+        if self.pool is not None:  # start the workers' interpreters before the clock does
+            self.pool.map(int, range(procs), chunksize=1)
+
+    def run(self, utts):
+        t0 = time.perf_counter()
+        res = [_worker(b) for b in utts] if self.pool is None else self.pool.map(_worker, list(utts), chunksize=1)
+        return time.perf_counter() - t0, [r[1] for r in res]
+
+    def close(self):
+        if self.pool is not None:
+            self.pool.close()
+            self.pool.join()
+            self.pool = None
 
 
 def decode_many_cpu(logp, tables, cfg, utts, positions, procs):
-    """``utts`` utterance indices, one reference process per host core (job-level sharding as ``egs2/*/asr.sh``
-    ``inference_nj``, one torch thread each).  ``tables (positions, B*beam, V)``.  Returns (wall seconds, results)."""
-    import multiprocessing as mp
-
-    W = cfg["beam"]
-    jobs = [(logp[b].numpy(), tables[:positions, b * W : (b + 1) * W].contiguous().numpy(), cfg, positions) for b in utts]
-    t0 = time.perf_counter()
-    if procs <= 1:
-        res = [_worker(j) for j in jobs]
-    else:
-        with mp.get_context("fork").Pool(procs) as pool:
-            res = pool.map(_worker, jobs, chunksize=1)
-    return time.perf_counter() - t0, [r[1] for r in res]
+    """``utts`` utterance indices over ``procs`` reference processes.  ``tables (positions, B*beam, V)``.
+    Returns (wall seconds, results)."""
+    pool = CpuPool(logp, tables, cfg, positions, procs)
+    try:
+        return pool.run(utts)
+    finally:
+        pool.close()

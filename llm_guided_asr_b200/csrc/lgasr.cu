@@ -61,7 +61,8 @@ struct lgasr_handle {
   StepLaunch sl2;    // k_step2 launch geometry
   size_t smem_step2;
   int cluster2;      // k_step2 launched as clusters of `beam` CTAs
-  int nth2;          // threads per CTA of k_step2 (256, 128 or 64)
+  int nth2;          // threads per CTA of k_step2 (256 or 128)
+  int mb2;           // its resident-CTA target per SM (launch bound): 5 (256 threads), 6, or 8 = the dense instance
   std::vector<void*> allocs;
   std::vector<long long> primer;
   std::vector<int> xlens;
@@ -117,20 +118,21 @@ static int dalloc(lgasr_handle* h, T** p, size_t n) {
 
 // instances of k_step2 for a CTA size: [0..3] single CTAs (general, one matrix, two matrices, one matrix + trace),
 // [4..7] the same as thread-block clusters
-template <int NTH>
+template <int NTH, int MB>
 static void step2_instances_of(const void** f) {
-  f[0] = (const void*)k_step2<NTH, false, 0, false>;
-  f[1] = (const void*)k_step2<NTH, false, 1, false>;
-  f[2] = (const void*)k_step2<NTH, false, 2, false>;
-  f[3] = (const void*)k_step2<NTH, false, 1, true>;
-  f[4] = (const void*)k_step2<NTH, true, 0, false>;
-  f[5] = (const void*)k_step2<NTH, true, 1, false>;
-  f[6] = (const void*)k_step2<NTH, true, 2, false>;
-  f[7] = (const void*)k_step2<NTH, true, 1, true>;
+  f[0] = (const void*)k_step2<NTH, false, 0, false, MB>;
+  f[1] = (const void*)k_step2<NTH, false, 1, false, MB>;
+  f[2] = (const void*)k_step2<NTH, false, 2, false, MB>;
+  f[3] = (const void*)k_step2<NTH, false, 1, true, MB>;
+  f[4] = (const void*)k_step2<NTH, true, 0, false, MB>;
+  f[5] = (const void*)k_step2<NTH, true, 1, false, MB>;
+  f[6] = (const void*)k_step2<NTH, true, 2, false, MB>;
+  f[7] = (const void*)k_step2<NTH, true, 1, true, MB>;
 }
-static void step2_instances(int nth, const void** f) {
-  if (nth == 256) step2_instances_of<256>(f);
-  else step2_instances_of<128>(f);  // 64 threads per CTA were measured too (slower: profiles/README.md) and dropped
+static void step2_instances(int nth, int mb, const void** f) {
+  if (nth == 256) step2_instances_of<256, 5>(f);
+  else if (mb == 8) step2_instances_of<128, 8>(f);
+  else step2_instances_of<128, 6>(f);  // 64 threads per CTA were measured too (slower: profiles/README.md) and dropped
 }
 
 extern "C" int lgasr_version(void) { return LGASR_VERSION; }
@@ -435,17 +437,40 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
   }
   // ---- k_step2 geometry: 6 scan rows of Tp + 4 floats, arena = pending keys | candidate rows | selection scratch ----
   {
-    // k_step2 serves the term matrices k_step cannot read (bf16 storage, per-row normalisers: lgasr_step_ex);
-    // LGASR_V2=1 routes every fused launch through it (it is a little slower than k_step on plain fp32 matrices)
+    // k_step2 serves the term matrices k_step cannot read (bf16 storage, per-row normalisers: lgasr_step_ex) and the
+    // plain fp32 launches it is faster on: a STREAMED row set (more than one chunk: two matrices at V = 5000, the
+    // OWSM vocabulary) in a grid of several waves - its row stream runs on every warp with the rows prefetched into L2
+    // (measured, profiles/r02x_shape_probe.txt: 123 vs 144 us per replay launch at configs[4]'s B = 512 with two
+    // matrices, 73 vs 95 us on the OWSM shape at B = 128; one-chunk rows and one-wave grids stay with k_step: 18.1 vs
+    // 19.2 us at configs[1]).  LGASR_V2=1 / 0 forces it on / off for every plain launch.
     const char* v2 = getenv("LGASR_V2");
     h->v2_all = (v2 && v2[0] == '1') ? 1 : 0;
+    if (!(v2 && (v2[0] == '0' || v2[0] == '1')) && h->fused && h->sl.nchunks > 1 && !h->seq_ok) h->v2_all = 1;
     h->v2 = h->fused ? 1 : 0;
     if (h->v2) {
       StepLaunch& sl = h->sl2;
       sl = h->sl;
       const long long selw = utt_select_smem_floats(d.W, d.R, d.NS);
+      // threads per CTA: the glue is paid per warp, so fewer, fatter warps issue fewer instructions per hypothesis
+      {
+        const char* nt = getenv("LGASR_NTH");
+        h->nth2 = 128;  // measured: 128 threads per CTA beat 256 and 64 on the stepping launches (profiles/r02e)
+        if (nt && (atoi(nt) == 128 || atoi(nt) == 256)) h->nth2 = atoi(nt);
+      }
+      // dense instance: a grid of several waves over streamed rows is bound by how many CTAs an SM holds (measured at
+      // configs[4]'s B = 512 with two matrices, profiles/r02y_occupancy_probe.txt: 143 / 133 / 125 us per stepping launch
+      // with 5 / 6 / 8 CTAs per SM): 64 registers per thread and the candidate rows in two groups (12 KB arena)
+      int sms2 = 0, dev2 = 0;
+      cudaGetDevice(&dev2);
+      cudaDeviceGetAttribute(&sms2, cudaDevAttrMultiProcessorCount, dev2);
+      const int V4b = (d.V + 3) & ~3;
+      bool dense = h->nth2 == 128 && d.mode == kModePreBeam && (long long)(d.K > 0 ? d.K : 1) * V4b > 6144 &&
+                   (long long)d.B * d.W > 6LL * sms2;
+      if (const char* de = getenv("LGASR_DENSE")) dense = h->nth2 == 128 && de[0] == '1';
+      h->mb2 = h->nth2 == 256 ? 5 : (dense ? 8 : 6);
       long long arena = (long long)n_sel * d.Tp;
-      if (arena > 6144) arena = 6144;
+      const long long acap = dense ? 3072 : 6144;
+      if (arena > acap) arena = acap;
       if (arena < d.Tp) arena = d.Tp;
       if (d.mode != kModePreBeam) arena = 0;
       if (arena < 2 * kPend2) arena = 2 * kPend2;
@@ -467,19 +492,13 @@ extern "C" int lgasr_create(const lgasr_config* c, lgasr_handle** out) {
       }
       // the attributes are per device: set them for every handle (cheap) instead of tracking high-water marks
       cudaError_t e = cudaSuccess;
-      // threads per CTA: the glue is paid per warp, so large grids (several waves) take fewer, fatter warps
-      {
-        const char* nt = getenv("LGASR_NTH");
-        h->nth2 = 128;  // measured: 128 threads per CTA beat 256 and 64 on the stepping launches (profiles/r02e)
-        if (nt && (atoi(nt) == 128 || atoi(nt) == 256)) h->nth2 = atoi(nt);
-      }
       const void* fns[8];
-      step2_instances(h->nth2, fns);
+      step2_instances(h->nth2, h->mb2, fns);
       static size_t hw2[64][3] = {};
       int dev_id = 0;
       cudaGetDevice(&dev_id);
       dev_id = dev_id < 0 || dev_id >= 64 ? 0 : dev_id;
-      size_t& cur2 = hw2[dev_id][h->nth2 == 256 ? 0 : h->nth2 == 128 ? 1 : 2];
+      size_t& cur2 = hw2[dev_id][h->nth2 == 256 ? 0 : h->mb2 == 6 ? 1 : 2];
       // (the cluster instances get the attribute with the selection buffer included; a later fall-back to single CTAs
       // launches with less, which is fine)
       if (h->smem_step2 > cur2) {
@@ -755,7 +774,7 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     cfg.dynamicSmemBytes = h->smem_step2;
     const bool trc = d.trace != nullptr && sl.row_path == 1;  // the stamped instance exists for the one-matrix path
     const void* fns[8];
-    step2_instances(h->nth2, fns);
+    step2_instances(h->nth2, h->mb2, fns);
     const void* kern = fns[(use_cluster ? 4 : 0) + (trc ? 3 : sl.row_path)];
     cfg.blockDim = dim3(h->nth2);
     void* args[5] = {(void*)&d, (void*)&tm, (void*)&sl, (void*)&h->pp, (void*)&h->rp};

@@ -19,10 +19,10 @@
 //      (ctc_prefix_score.py          scans over the frames (r^n, then r_sum; three frames per thread) give the
 //       :122-160, scorers/           survivor's state.  The fix-up pass of the second scan writes the state AND the
 //       ctc.py:56-62)                frame-shifted phi arrays of phase 4: there is no epilogue pass.
-//   4. log psi + records          one candidate per half warp, ONE sweep: sum_t exp(phi[t-1] + x[t] - M) with M the
-//      (:163-185,                    maximum of phi (x <= 0, so no term exceeds 1); exact two-sweep fallback for a
-//       batch_beam_search.py         candidate whose sum leaves the fp32 range; total = (fused + w_ctc*(psi - s_prev))
-//       :313-318)                    + score.
+//   4. log psi + records          one candidate per half warp, max / sum-of-exp sweeps over float4 rows of
+//      (:163-185,                    phi[t-1] + x[t] (torch.logsumexp's order of operations);
+//       batch_beam_search.py         total = (fused + w_ctc*(psi - s_prev)) + score.
+//       :313-318)
 //   5. exchange + selection       thread-block cluster (distributed shared memory) or L2 ticket, then utt_select
 //                                    (global top-beam, post_process, end_detect).
 //
@@ -45,7 +45,6 @@ struct __align__(16) Step2Smem {
   int4 m_h0;                            // (parent slot, last token, parent's last token, run_slot)
   int4 m_h1;                            // (s_prev, score, 0, 0) as bits
   float m_sc[kMaxTerms + 4];            // per-scorer cumulative scores (cluster exchange only)
-  unsigned wm[2][kStepWarps];           // per-warp maxima (ordered) of the two phi arrays; 16-byte aligned
   int pend_cnt[2], overflow[2];         // double-buffered by merge iteration
   float w_eos, psi_eos;
   int last_flag, pad0;
@@ -456,8 +455,10 @@ __device__ __forceinline__ float scan_prefix(float cur, float A, float y0, int t
 // TR: debug instance with clock64 / globaltimer stamps (LGASR_TRACE=1)
 // NTH: threads per CTA (256, 128 or 64).  The glue around the streaming loops is paid per warp, so fewer, fatter warps
 // issue fewer instructions per hypothesis (the choice is made in lgasr.cu from the grid size).
-template <int NTH, bool CL, int NT, bool TR>
-__global__ void __launch_bounds__(NTH, NTH == 64 ? 6 : 5)
+// MB: resident CTAs per SM the register allocation aims at (5 with 256 threads, 6 or 8 with 128; lgasr.cu picks 8 - with
+// the candidate rows in two groups - for grids of several waves over streamed rows)
+template <int NTH, bool CL, int NT, bool TR, int MB>
+__global__ void __launch_bounds__(NTH, MB)
     k_step2(const __grid_constant__ Dev d, const __grid_constant__ Terms tm, const __grid_constant__ StepLaunch sl, int pp, int rp) {
   constexpr int NW = NTH / 32;
   constexpr int G1 = NTH == 256 ? 5 : 10, G2 = NTH == 256 ? 2 : 5, G0 = NTH == 256 ? 2 : 4;
@@ -569,12 +570,10 @@ __global__ void __launch_bounds__(NTH, NTH == 64 ? 6 : 5)
   // ======================= phase 3: CTC state of this hypothesis ===============================================
   const float* p0 = bR0;  // phi arrays of phase 4 (frame-shifted): P0[u] = r_sum[u-1], P1[u] = r^b[u-1]
   const float* p1 = bR1;
-  float M0 = 0.f, M1 = 0.f;
   if (d.use_ctc) {
     float* r_out = d.r[rp ^ 1] + ((long long)row * 2) * Tp;
     mbar_wait(reinterpret_cast<uint64_t*>(&S->bar_ctc), 0);
     LGASR_T2(2, clock64());
-    float m0 = LGASR_NEG, m1 = LGASR_NEG;
     if (has_parent) {
       const int olen_par = olen - 1;
       const int start = olen_par > 1 ? olen_par : 1;              // first frame of the recursion that makes this state
@@ -651,15 +650,9 @@ __global__ void __launch_bounds__(NTH, NTH == 64 ? 6 : 5)
         r_out[Tp + t] = rs;
         bR0[t + 1] = rs;
         bR1[t + 1] = rb;
-        if (t + 1 < T) {  // entries a candidate sum can reach
-          m0 = fmaxf(m0, rs);
-          m1 = fmaxf(m1, rb);
-        } else {
-          S->psi_eos = rs;  // t == T - 1: r_sum at the end frame (:180-181)
-        }
+        if (t + 1 >= T) S->psi_eos = rs;  // t == T - 1: r_sum at the end frame (:180-181)
         prev = rs;
       }
-      if (tid == 0) m0 = fmaxf(m0, rn0);  // P0[start] = r_sum[start-1]
     } else {
       // initial hypothesis (position 0): the state is given; phi arrays staged in bN / bS
       const int pstart = olen > 1 ? olen : 1;  // a primer makes the first prefix longer than [sos]
@@ -668,35 +661,17 @@ __global__ void __launch_bounds__(NTH, NTH == 64 ? 6 : 5)
         const float rs = in ? bR1[u - 1] : LGASR_NEG;
         bN[u] = rs;
         bS[u] = rs;  // r^b == r_sum while r^n is log-zero (:82-93)
-        if (in) m0 = fmaxf(m0, rs);
         if (u < T) {
           r_out[u] = bR0[u];
           r_out[Tp + u] = bR1[u];
         }
       }
-      m1 = m0;
       if (tid == 0) S->psi_eos = bR1[T - 1];
       p0 = bN;
       p1 = bS;
     }
-    // maxima of the phi arrays: ordered-integer warp reductions, one shared word per warp
-    const unsigned o0 = __reduce_max_sync(FULLMASK, f2ord(m0)), o1 = __reduce_max_sync(FULLMASK, f2ord(m1));
-    if (lane == 0) {
-      S->wm[0][warp] = o0;
-      S->wm[1][warp] = o1;
-    }
     __syncthreads();  // state + phi arrays complete
     LGASR_T2(3, clock64());
-    {
-      unsigned a = S->wm[0][0], c = S->wm[1][0];
-#pragma unroll
-      for (int w2 = 1; w2 < NW; ++w2) {
-        a = max(a, S->wm[0][w2]);
-        c = max(c, S->wm[1][w2]);
-      }
-      M0 = ord2f(a);
-      M1 = ord2f(c);
-    }
   } else {
     __syncthreads();
   }
@@ -766,48 +741,33 @@ __global__ void __launch_bounds__(NTH, NTH == 64 ? 6 : 5)
         const int jr = g0 + (have ? i : 0);
         const int c = key_idx(tk[jr]);
         const bool special = (c == d.eos) || (d.eos != d.blank && c == d.blank);
-        // log psi = logsumexp({phi[t-1] + x[t] : start <= t < T} U {r^n[start-1]})  (:163-171).  phi is pre-shifted and
-        // log-zero outside [start, T), so the sum runs over whole float4 rows.  ONE sweep: every term is taken
-        // relative to M = max(phi) (x <= 0, so no term exceeds 1).  (A special or missing candidate runs the same code
-        // on whatever its arena slot holds and discards the result.)
+        // log psi = logsumexp({phi[t-1] + x[t] : start <= t < T} U {r^n[start-1]})  (:163-171), the way torch.logsumexp
+        // does it (max, sum of exp, log): a one-sweep sum relative to max(phi) is 2-3 % faster but its roundings are
+        // independent of the reference's (max |dscore| against the reference 9e-5 instead of 3e-5 after 64 positions).
+        // phi is pre-shifted and log-zero outside [start, T), so the sums run over whole float4 rows.  (A special or
+        // missing candidate runs the same code on whatever its arena slot holds and discards the result.)
         const float4* x4 = reinterpret_cast<const float4*>(arena + (jr - g0) * Tp);
-        const bool rp1 = (c == last);
-        const float4* p4 = reinterpret_cast<const float4*>(rp1 ? p1 : p0);
+        const float4* p4 = reinterpret_cast<const float4*>((c == last) ? p1 : p0);
         const float rn0 = (olen == 0) ? arena[(jr - g0) * Tp] : LGASR_LOGZERO;
-        const float M = fmaxf(rp1 ? M1 : M0, rn0);
-        const float mML = -M * kL2E;
-        float sum = (hl == 0) ? ex2_approx(fmaf(rn0, kL2E, mML)) : 0.f;
+        float m = rn0;
 #pragma unroll 2
         for (int q = hl; q < nq4; q += 16) {
           const float4 xa = x4[q], pa = p4[q];
-          sum += ex2_approx(fmaf(pa.x + xa.x, kL2E, mML)) + ex2_approx(fmaf(pa.y + xa.y, kL2E, mML)) +
-                 ex2_approx(fmaf(pa.z + xa.z, kL2E, mML)) + ex2_approx(fmaf(pa.w + xa.w, kL2E, mML));
+          m = fmaxf(fmaxf(fmaxf(m, pa.x + xa.x), fmaxf(pa.y + xa.y, pa.z + xa.z)), pa.w + xa.w);
+        }
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULLMASK, m, o));
+        // (e - m) first: the subtraction is exact near the maximum, where the terms matter
+        float sum = (hl == 0) ? ex2_approx((rn0 - m) * kL2E) : 0.f;
+#pragma unroll 2
+        for (int q = hl; q < nq4; q += 16) {
+          const float4 xa = x4[q], pa = p4[q];
+          sum += ex2_approx((pa.x + xa.x - m) * kL2E) + ex2_approx((pa.y + xa.y - m) * kL2E) +
+                 ex2_approx((pa.z + xa.z - m) * kL2E) + ex2_approx((pa.w + xa.w - m) * kL2E);
         }
 #pragma unroll
         for (int o = 8; o >= 1; o >>= 1) sum += __shfl_xor_sync(FULLMASK, sum, o);
-        float psi = M + logf(sum);
-        // a candidate whose every frame is far below the hypothesis' own mass (or x > 0 somewhere): exact two sweeps
-        const bool bad = !special && have && !(sum > 1e-30f && sum < 1e30f);
-        if (__any_sync(FULLMASK, bad)) {
-          float m = rn0;
-#pragma unroll 1
-          for (int q = hl; q < nq4; q += 16) {
-            const float4 xa = x4[q], pa = p4[q];
-            m = fmaxf(fmaxf(fmaxf(m, pa.x + xa.x), fmaxf(pa.y + xa.y, pa.z + xa.z)), pa.w + xa.w);
-          }
-#pragma unroll
-          for (int o = 8; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULLMASK, m, o));
-          float s2 = (hl == 0) ? ex2_approx((rn0 - m) * kL2E) : 0.f;
-#pragma unroll 1
-          for (int q = hl; q < nq4; q += 16) {
-            const float4 xa = x4[q], pa = p4[q];
-            s2 += ex2_approx((pa.x + xa.x - m) * kL2E) + ex2_approx((pa.y + xa.y - m) * kL2E) +
-                  ex2_approx((pa.z + xa.z - m) * kL2E) + ex2_approx((pa.w + xa.w - m) * kL2E);
-          }
-#pragma unroll
-          for (int o = 8; o >= 1; o >>= 1) s2 += __shfl_xor_sync(FULLMASK, s2, o);
-          if (bad) psi = m + logf(s2);
-        }
+        float psi = m + logf(sum);
         if (c == d.eos)
           psi = psi_eos;
         else if (special)

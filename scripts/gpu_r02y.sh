@@ -1,9 +1,10 @@
 #!/bin/bash
-# r02y: ncu --set full capture of the stepping k_step instance at B = 512, after the same command ran clean
-O=gpurun_out/r02y; mkdir -p $O
-timeout 300 python scripts/step_probe.py --B 512 --mode step --reps 2 > $O/plain512.log 2>&1; rc=$?; cat $O/plain512.log | cut -c1-200
-if [ $rc -eq 0 ]; then
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_step -s 14 -c 1 -o $O/step512 \
-    python scripts/step_probe.py --B 512 --mode step --reps 2 > $O/ncu512.log 2>&1; echo "ncu rc=$?"
-fi
-ls -la $O
+# r02y3: dense k_step2 instance: whole GPU suite with it forced on every launch, then the default routing (suite + probes)
+O=gpurun_out/r02y3; mkdir -p $O
+LGASR_V2=1 LGASR_DENSE=1 timeout 1500 python -m pytest tests -m gpu -q > $O/pytest_dense.log 2>&1; echo "rc=$?" >> $O/pytest_dense.log; tail -4 $O/pytest_dense.log
+LGASR_V2=1 timeout 1500 python -m pytest tests -m gpu -q > $O/pytest_v2.log 2>&1; echo "rc=$?" >> $O/pytest_v2.log; tail -3 $O/pytest_v2.log
+timeout 1500 python -m pytest tests -m gpu -q > $O/pytest.log 2>&1; echo "rc=$?" >> $O/pytest.log; tail -3 $O/pytest.log
+timeout 300 python scripts/step_probe.py --B 64 512 --K 2 > $O/probe.txt 2>&1
+timeout 300 python scripts/step_probe.py --B 64 512 --K 1 >> $O/probe.txt 2>&1
+timeout 300 python scripts/step_probe.py --B 32 128 --K 2 --shape owsm --L 6 >> $O/probe.txt 2>&1
+cut -c1-175 $O/probe.txt
