@@ -407,7 +407,8 @@ def run_configs4(rank, world, dev, cfg, n_utts=4096, batch=512, K=2, reps=2):
         eng.set_posteriors(logps[bi], [lengths[i] for i in idx])
         eng.begin([L] * Bb, [0] * Bb, [eos])
         eng.replay([[t[i][: Bb * W] for t in tabs] for i in range(L)], consts, wts, ld=V)
-        return eng.gather_best  # deferred read-back (sharding.decode_sharded calls it after queueing the next batch)
+        # deferred read-back (sharding.decode_sharded calls it after queueing the next batch), as arrays
+        return lambda: sharding.PackedBest(*eng.gather_best_arrays())
 
     times = []
     merged = None
@@ -429,14 +430,15 @@ def run_configs4(rank, world, dev, cfg, n_utts=4096, batch=512, K=2, reps=2):
     if rank != 0:
         return None
     sec = float(t[0])
-    ok = merged is not None and [r[0] for r in merged] == list(range(n_utts)) and all(len(r[1]) == L + 2 for r in merged)
+    ok = (merged is not None and len(merged) == n_utts and bool((merged.indices == np.arange(n_utts)).all())
+          and bool((merged.lengths == L + 2).all()) and merged[n_utts - 1][0] == n_utts - 1 and len(merged[0][1]) == L + 2)
     summ = sharding.shard_summary(lengths, world)
     return {
         "workload": f"configs[4]: {n_utts} synthetic utterances, T in [299, 374] (jittered), V={V}, beam={W}, pre-beam={cfg['S']}, {K} full-scorer matrices, {L} positions, batches of <= {batch} utterances per handle",
         "value": n_utts / sec, "unit": "utts/s", "scaling": "strong", "seconds": sec, "n_gpus": world,
         "utts_per_rank": summ["count"], "frames_per_rank": summ["frames"],
         "all_utterances_returned_in_order": bool(ok),
-        "through": "sharding.partition / batches / decode_sharded -> FusedStepEngine.set_posteriors / begin / replay / gather_best; final gather of (index, tokens, score) records to rank 0 inside the timed region",
+        "through": "sharding.partition / batches / decode_sharded -> FusedStepEngine.set_posteriors / begin / replay / gather_best_arrays; final gather of (index, tokens, score) records to rank 0 inside the timed region",
     }
 
 

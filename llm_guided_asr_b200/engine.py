@@ -213,9 +213,9 @@ class FusedStepEngine:
                 )
             )
 
-    def gather_best(self, normalize_length: bool = False):
-        """Best ended hypothesis of every utterance in one call (``lgasr_gather_best``): list of
-        ``(tokens, score)``; ``([], 0.0)`` where nothing ended."""
+    def gather_best_arrays(self, normalize_length: bool = False):
+        """``lgasr_gather_best`` as arrays: ``tokens (B, L)`` int64, ``lens (B,)`` int32 (0 where nothing ended),
+        ``scores (B,)`` float32 - no per-token Python objects (the sharded driver's result path)."""
         B = self.cfg.n_utts
         ml = self.cfg.primer_len + self.cfg.max_len_cap + 1
         toks = np.empty((B, ml), dtype=np.int64)
@@ -228,7 +228,13 @@ class FusedStepEngine:
                     score.ctypes.data_as(_lib._PF), _stream_ptr(self.device),
                 )
             )
-        return [(toks[b, : lens[b]].tolist(), float(score[b])) for b in range(B)]
+        return toks, lens, score
+
+    def gather_best(self, normalize_length: bool = False):
+        """Best ended hypothesis of every utterance in one call (``lgasr_gather_best``): list of
+        ``(tokens, score)``; ``([], 0.0)`` where nothing ended."""
+        toks, lens, score = self.gather_best_arrays(normalize_length)
+        return [(toks[b, : lens[b]].tolist(), float(score[b])) for b in range(len(lens))]
 
     def reorder_rows(self, dst: torch.Tensor, src: torch.Tensor, row_elems: Optional[int] = None):
         """``dst[o, b*W + j, :n] = src[o, b*W + parent[b][j], :n]`` for the hypotheses that survived the last

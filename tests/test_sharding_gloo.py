@@ -85,3 +85,48 @@ def test_world2_gloo_equals_single_process():
         assert p.exitcode == 0
     assert got[1] is None
     assert got[0] == single  # tokens bit-exact, scores identical (same code on every rank)
+
+
+def _decode_fn_packed(batch):
+    """The array path (what FusedStepEngine.gather_best_arrays feeds): deferred read-back returning a PackedBest."""
+    res = [_decode_one(i) for i in batch]
+    width = max(len(t) for t, _ in res) + 2  # wider than any hypothesis, like the engine's (B, maxlen) buffer
+    toks = np.full((len(res), width), 12345, dtype=np.int64)
+    for r, (t, _) in enumerate(res):
+        toks[r, : len(t)] = t
+    pb = sharding.PackedBest(toks, [len(t) for t, _ in res], [s for _, s in res])
+    return lambda: pb
+
+
+def _worker_packed(rank, world, port, q, lengths):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        out = sharding.decode_sharded(_decode_fn_packed, lengths, batch_size=2)
+        q.put((rank, None if out is None else out.to_list()))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [len(LENGTHS), 1])
+def test_world2_gloo_packed_arrays_equal_list_path(n):
+    """Arrays end to end (no per-token Python objects), deferred read-back; n = 1 leaves rank 1 with an empty shard,
+    which must still take part in the gather."""
+    lengths = LENGTHS[:n]
+    single = sharding.decode_sharded(_decode_fn, lengths, batch_size=2, rank=0, world=1)
+    packed1 = sharding.decode_sharded(_decode_fn_packed, lengths, batch_size=2, rank=0, world=1)
+    assert isinstance(packed1, sharding.PackedRecords) and packed1.to_list() == [(i, t, np.float32(s)) for i, t, s in single]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_packed, args=(r, 2, port, q, lengths)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[1] is None
+    assert got[0] == packed1.to_list()
