@@ -336,36 +336,59 @@ def launch_time_us(eng, mats, consts, wts, V, mode, reps, first=1):
     return statistics.mean(out[1:]), n * reps
 
 
-def roofline_b512(dev, cfg, peak, reps=3):
-    """The same kernel with configs[4]'s per-GPU batch in flight (512 utterances, device-generated inputs, 16 positions):
-    several waves of CTAs, ticket exchange."""
+def roofline_shape(dev, cfg, peak, B, K=1, L=16, T=None, V=None, W=None, S=None, what="", reps=3):
+    """The step kernel on another BASELINE shape / batch (device-generated inputs, L positions): stepping launches and
+    the graph replay, algorithmic bytes of SURVEY.md 8(d) for that shape."""
     from llm_guided_asr_b200.engine import FusedStepEngine
 
-    B, T, V, W, L = 512, cfg["T"], cfg["V"], cfg["beam"], 16
+    T, V, W, S = T or cfg["T"], V or cfg["V"], W or cfg["beam"], S or cfg["S"]
+    c = dict(cfg, B=B, T=T, V=V, beam=W, S=S, K=K)
     g = torch.Generator(device=dev).manual_seed(7)
     logp = torch.log_softmax(3.0 * torch.randn(B, T, V, device=dev, generator=g), dim=-1)
-    tables = torch.log_softmax(2.0 * torch.randn(L, B * W, V, device=dev, generator=g), dim=-1)
-    eng = FusedStepEngine(B, T, V, W, cfg["S"], ["decoder"], "full", True, cfg["ctc_weight"], V - 1, V - 1, L, 1, False, device=dev)
+    tabs = [torch.log_softmax(2.0 * torch.randn(L, B * W, V, device=dev, generator=g), dim=-1) for _ in range(K)]
+    names = ["decoder", "lm"][:K]
+    wts = [1.0 - cfg["ctc_weight"], 0.5][:K]
+    eng = FusedStepEngine(B, T, V, W, S, names, "full", True, cfg["ctc_weight"], V - 1, V - 1, L, 1, False, device=dev)
     eng.set_posteriors(logp, [T] * B)
-    mats = [[tables[i]] for i in range(L)]
-    wts = [1.0 - cfg["ctc_weight"]]
-    us_step, n1 = launch_time_us(eng, mats, [0.0], wts, V, "step", reps)
-    us_rep, _ = launch_time_us(eng, mats, [0.0], wts, V, "replay", reps)
-    ab = B * (4 * (T * (W * cfg["S"] + 1 + 4 * W) + cfg["K"] * W * V) + 16 * W)  # T_eff ~ T for the first positions
+    mats = [[t[i] for t in tabs] for i in range(L)]
+    us_step, n1 = launch_time_us(eng, mats, [0.0] * K, wts, V, "step", reps)
+    us_rep, _ = launch_time_us(eng, mats, [0.0] * K, wts, V, "replay", reps)
     nrun = [[1] * B] + [[W] * B] * (L - 1)
-    ab_step = algorithmic_bytes(dict(cfg, B=B), nrun[1:]) / (L - 1)
-    ab_rep = algorithmic_bytes(dict(cfg, B=B), nrun) / L
+    ab_step = algorithmic_bytes(c, nrun[1:]) / (L - 1)
+    ab_rep = algorithmic_bytes(c, nrun) / L
     info = eng.launch_info()
     eng.close()
-    del logp, tables
+    del logp, tabs, mats
     torch.cuda.empty_cache()
     return {
-        "bound": "hbm", "kernel": "k_step (stepping launches)", "utterances_in_flight": B,
+        "bound": "hbm", "kernel": "step kernel (stepping launches)", "shape": what, "utterances_in_flight": B,
+        "T": T, "V": V, "beam": W, "pre_beam": S, "full_scorer_matrices": K,
         "achieved": ab_step / us_step / 1e3, "peak": peak, "unit": "GB/s", "frac": ab_step / us_step / 1e3 / peak,
         "avg_launch_us": us_step, "algorithmic_bytes_per_launch": ab_step,
         "replay": {"avg_launch_us": us_rep, "achieved": ab_rep / us_rep / 1e3, "frac": ab_rep / us_rep / 1e3 / peak},
         "launches_timed": n1, "k_step": info,
     }
+
+
+def roofline_b512(dev, cfg, peak, reps=3):
+    """configs[1]'s shape with configs[4]'s per-GPU batch in flight (512 utterances, one matrix): several waves of CTAs,
+    ticket exchange (k_step)."""
+    r = roofline_shape(dev, cfg, peak, 512, K=1, L=16, what="configs[1] shape, 512 utterances in flight", reps=reps)
+    r["kernel"] = "k_step (stepping launches)"
+    return r
+
+
+def roofline_other_shapes(dev, cfg, peak):
+    """The shapes whose row sets are streamed: configs[4]'s per-GPU batch (two matrices, 512 utterances: k_step2, dense
+    instance) and configs[3] OWSM (T = 749, V = 50 000, beam 5, pre-beam 7, two matrices, 128 utterances: k_step2)."""
+    out = []
+    for kw in (dict(B=512, K=2, L=12, what="configs[4] per-GPU batch: configs[2] shape (decoder + LM matrices), 512 utterances in flight"),
+               dict(B=128, K=2, L=6, T=749, V=50000, W=5, S=7, what="configs[3] OWSM shape, 128 utterances in flight")):
+        try:
+            out.append(roofline_shape(dev, cfg, peak, **kw))
+        except Exception as e:  # informative legs: never fail the bench line on them
+            out.append({"shape": kw["what"], "unavailable": repr(e)[:200]})
+    return out
 
 
 def run_configs4(rank, world, dev, cfg, n_utts=4096, batch=512, K=2, reps=2):
@@ -660,9 +683,10 @@ def run_ours(args, rank, world, local_rank):
         return
 
     # ---- rank 0, one GPU: the reference itself beside it (CPU on all host cores, GPU PyTorch) + parity ----------
-    cpu = parity = ref_gpu = b512 = real = None
+    cpu = parity = ref_gpu = b512 = real = shapes = None
     if args.gpus == 1 and not args.no_cpu:
         b512 = roofline_b512(dev, cfg, peak)
+        shapes = roofline_other_shapes(dev, cfg, peak)
         try:
             real = run_decode_real(dev, cfg)
         except Exception as e:  # informative leg: never fail the bench line on it
@@ -739,6 +763,7 @@ def run_ours(args, rank, world, local_rank):
                        "algorithmic_bytes_per_launch": ab_rep},
         },
         "roofline_b512": b512,
+        "roofline_other_shapes": shapes,
         "configs4": c4,
         "decode_real": real,
         "cpu_baseline": cpu,
