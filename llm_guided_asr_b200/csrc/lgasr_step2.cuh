@@ -461,7 +461,7 @@ template <int NTH, bool CL, int NT, bool TR, int MB>
 __global__ void __launch_bounds__(NTH, MB)
     k_step2(const __grid_constant__ Dev d, const __grid_constant__ Terms tm, const __grid_constant__ StepLaunch sl, int pp, int rp) {
   constexpr int NW = NTH / 32;
-  constexpr int G1 = NTH == 256 ? 5 : 10, G2 = NTH == 256 ? 2 : 5, G0 = NTH == 256 ? 2 : 4;
+  constexpr int G1 = (NTH == 256 || MB >= 8) ? 5 : 10, G2 = NTH == 256 ? 2 : 5, G0 = NTH == 256 ? 2 : 4;
   constexpr int GG = NT == 1 ? G1 : (NT == 2 ? G2 : G0);
   const int b = blockIdx.y, h = blockIdx.x;
   const int tid = threadIdx.x;
