@@ -800,7 +800,13 @@ static int step_impl(lgasr_handle* h, const Terms& tm, cudaStream_t st, bool pdl
     cfg.stream = st;
     cudaLaunchAttribute at[2];
     int na = 0;
-    if (pdl) {
+    // Stepping launches carry the attribute too: the CTAs' prologue (mbarrier set-up, parameter and metadata address
+    // arithmetic) then overlaps the tail of the previous kernel of the stream when that kernel lets its dependents go
+    // early (k_step, k_log_softmax_rows and k_score_filter do); everything that reads memory comes after
+    // griddepcontrol.wait, and after a kernel that never triggers this is an ordinary launch.  22.0 -> 20.0 us per
+    // launch at B = 64 (profiles/r02af_step_pdl_probe.txt).  LGASR_STEP_PDL=0 switches it off.
+    const char* spd = getenv("LGASR_STEP_PDL");
+    if (pdl || !(spd && spd[0] == '0')) {
       at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
       at[na].val.programmaticStreamSerializationAllowed = 1;
       ++na;

@@ -120,6 +120,9 @@ __global__ __launch_bounds__(kLsmThreads) void k_log_softmax_rows(const void* __
   __shared__ float red[kLsmThreads / 32];
   __shared__ float xm[16], xs[16];  // (max, sum) of every CTA of the cluster, written by the peers
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // a step kernel queued behind this one (programmatic launch) may set up its CTAs now; it reads the rows only after
+  // its griddepcontrol.wait, i.e. when this grid has completed
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const unsigned CS = cluster_nctarank(), c = cluster_ctarank();
   const long long r = blockIdx.y;
   const int v0 = (int)c * SL;
@@ -235,6 +238,7 @@ __global__ __launch_bounds__(kFilterThreads) void k_score_filter(const long long
                                                                  float* __restrict__ out, long long ld_out, int vec_ok) {
   __shared__ int s_has, s_cnt, s_lastpos;
   const int tid = threadIdx.x;
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // see k_log_softmax_rows
   const long long* y = yseq + blockIdx.x * ld_y;
   if (tid == 0) {
     s_has = 0;
