@@ -244,6 +244,21 @@ int lgasr_log_softmax_rows(const void* d_logits, int dtype, int64_t ld_in, float
  * bf16 read + fp32 write (log_softmax) + fp32 read (step) = 10 bytes per entry. */
 int lgasr_row_logsumexp(const void* d_logits, int dtype, int64_t ld_in, float* d_lse, int rows, int vocab, void* stream);
 
+/* lgasr_row_logsumexp for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same
+ * inputs, output and tolerance as lgasr_row_logsumexp, but a row is split over plain CTAs (no thread-block cluster)
+ * whose partial (max, sum) pairs meet in a FIXED scratch array inside the library (a file-scope __device__ array of
+ * 278 528 bytes that every GPU loading the library holds until exit); the call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine) - it queues one cudaMemsetAsync of the scratch tickets and one kernel on
+ * `stream`.  Limits: rows <= LGASR_NOALLOC_MAX_ROWS, vocab <= LGASR_NOALLOC_MAX_VOCAB, else LGASR_EINVAL with a message.
+ * Every call on a device shares the one scratch array: calls that OVERLAP on the GPU (different streams, or graph
+ * branches that may run concurrently) race on it - serialise them.  The first call on each device resolves the
+ * array's device address (cudaGetSymbolAddress); make that call once outside a capture. */
+#define LGASR_NOALLOC_MAX_ROWS 4096
+#define LGASR_NOALLOC_MAX_VOCAB (1 << 20)
+int lgasr_row_logsumexp_noalloc(const void* d_logits, int dtype, int64_t ld_in, float* d_lse, int rows, int vocab,
+                                void* stream);
+
 /* lgasr_step with typed term matrices: h_term_dtype[k] is LGASR_F32 or LGASR_BF16 (storage of matrix k);
  * h_term_norm[k] (may be NULL, and the array itself may be NULL) is a device array of B*beam fp32 normalisers:
  * the score of entry v of row r is float(matrix[r][v]) - norm[r], i.e. log_softmax(logits) when norm = logsumexp.

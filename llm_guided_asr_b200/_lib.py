@@ -73,6 +73,7 @@ PROTOTYPES = {
     "lgasr_reorder_rows": (_I, [_P, _P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _P]),
     "lgasr_log_softmax_rows": (_I, [_P, _I, _I64, _P, _I64, _I, _I, _P]),
     "lgasr_row_logsumexp": (_I, [_P, _I, _I64, _P, _I, _I, _P]),
+    "lgasr_row_logsumexp_noalloc": (_I, [_P, _I, _I64, _P, _I, _I, _P]),
     "lgasr_step_ex": (_I, [_P, C.POINTER(_P), _PI32, C.POINTER(_P), _PF, _PF, _I64, _P]),
     "lgasr_score_filter": (_I, [_P, _I64, _I, _I, _I, _I, _I, _I, _I, _I, _P, _I64, _P]),
 }

@@ -1453,3 +1453,176 @@ extern "C" int lgasr_score_filter(const int64_t* d_yseq, int64_t ld_y, int cur_l
   LAUNCH_CK();
   return LGASR_OK;
 }
+
+// ---- lgasr_row_logsumexp_noalloc ---------------------------------------------------------------------------------
+// No counterpart in the reference.  A variant of the row-logsumexp kernel
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it) and whose
+// launch path cannot use thread-block clusters: a long row is split over plain CTAs and the slices' (max, sum) pairs
+// meet in SCRATCH memory instead of the cluster's distributed shared memory.  The scratch is a file-scope device array
+// of fixed size: every GPU that loads the library holds it until exit, every call shares it (calls that overlap on the
+// GPU race on it), and it keeps the last call's contents - the tickets are cleared at the start of every call.
+constexpr int kNoAllocMaxRows = 4096;     // LGASR_NOALLOC_MAX_ROWS
+constexpr int kNoAllocMaxSplits = 8;
+constexpr int kNoAllocMaxVocab = 1 << 20;  // LGASR_NOALLOC_MAX_VOCAB
+constexpr int kNoAllocThreads = 256;
+struct NoAllocScratch {
+  float2 part[kNoAllocMaxRows][kNoAllocMaxSplits];  // (max, sum of exp relative to it) of every slice: 256 KB
+  int ticket[kNoAllocMaxRows];                      // slices of the row that have delivered: 16 KB, zero between calls
+};
+static __device__ __align__(256) NoAllocScratch g_noalloc_scratch;  // 278 528 bytes per GPU
+
+__device__ __forceinline__ void lse_merge(float& m, float& s, float m2, float s2) {
+  // (m, s) (+) (m2, s2) with s = sum exp(x - m); an empty side has m = -inf, s = 0
+  const float mm = fmaxf(m, m2);
+  if (mm == -INFINITY) return;
+  s = s * expf(m - mm) + s2 * expf(m2 - mm);
+  m = mm;
+}
+
+// grid (splits, rows).  `scr` is the DEVICE address of g_noalloc_scratch (cudaGetSymbolAddress on the host side).
+template <bool BF16, bool VEC>
+__global__ void __launch_bounds__(kNoAllocThreads) k_row_logsumexp_scratch(const void* __restrict__ logits, long long ld_in,
+                                                                          float* __restrict__ lse_out, int V, int SL,
+                                                                          NoAllocScratch* scr) {
+  const int r = blockIdx.y, sp = blockIdx.x, nsp = gridDim.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int e0 = sp * SL;
+  const int e1 = min(V, e0 + SL);
+  float m = -INFINITY, s = 0.f;
+  auto take = [&](float x) {
+    if (x > m) {
+      s = s * expf(m - x) + 1.f;  // expf(-inf) = 0 on the first element
+      m = x;
+    } else if (x > -INFINITY) {
+      s += expf(x - m);
+    }
+  };
+  if (BF16) {
+    const __nv_bfloat16* row = reinterpret_cast<const __nv_bfloat16*>(logits) + (long long)r * ld_in;
+    if (VEC) {  // SL % 8 == 0, 16-byte aligned rows
+      const uint4* p = reinterpret_cast<const uint4*>(row + e0);
+      const int nq = (e1 - e0) >> 3;
+      for (int q = tid; q < nq; q += kNoAllocThreads) {
+        const uint4 u = __ldg(p + q);
+        const unsigned w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          take(__uint_as_float(w[k] << 16));
+          take(__uint_as_float(w[k] & 0xffff0000u));
+        }
+      }
+      for (int e = e0 + (nq << 3) + tid; e < e1; e += kNoAllocThreads) take(__bfloat162float(row[e]));
+    } else {
+      for (int e = e0 + tid; e < e1; e += kNoAllocThreads) take(__bfloat162float(row[e]));
+    }
+  } else {
+    const float* row = reinterpret_cast<const float*>(logits) + (long long)r * ld_in;
+    if (VEC) {
+      const float4* p = reinterpret_cast<const float4*>(row + e0);
+      const int nq = (e1 - e0) >> 2;
+      for (int q = tid; q < nq; q += kNoAllocThreads) {
+        const float4 v = __ldg(p + q);
+        take(v.x);
+        take(v.y);
+        take(v.z);
+        take(v.w);
+      }
+      for (int e = e0 + (nq << 2) + tid; e < e1; e += kNoAllocThreads) take(__ldg(row + e));
+    } else {
+      for (int e = e0 + tid; e < e1; e += kNoAllocThreads) take(__ldg(row + e));
+    }
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, m, o), s2 = __shfl_xor_sync(0xffffffffu, s, o);
+    lse_merge(m, s, m2, s2);
+  }
+  __shared__ float2 wred[kNoAllocThreads / 32];
+  __shared__ int is_last;
+  if (lane == 0) wred[warp] = make_float2(m, s);
+  __syncthreads();
+  if (tid == 0) {
+    m = wred[0].x;
+    s = wred[0].y;
+    for (int w = 1; w < kNoAllocThreads / 32; ++w) lse_merge(m, s, wred[w].x, wred[w].y);
+    scr->part[r][sp] = make_float2(m, s);
+    __threadfence();  // the pair is visible before the ticket is
+    const int t = atomicAdd(&scr->ticket[r], 1);
+    is_last = (t == nsp - 1);
+    if (is_last) {
+      __threadfence();
+      // the last slice to arrive combines all of them, in slice order (the result does not depend on arrival order)
+      float M = -INFINITY, S = 0.f;
+      for (int i = 0; i < nsp; ++i) {
+        const float2 p = __ldcg(&scr->part[r][i]);
+        lse_merge(M, S, p.x, p.y);
+      }
+      lse_out[r] = (M == -INFINITY) ? -INFINITY : M + logf(S);
+      scr->ticket[r] = 0;  // left clean for the next call (which clears the tickets again anyway)
+    }
+  }
+}
+
+// Device address of g_noalloc_scratch, resolved once per device with that device current.  (In host code the array's
+// name is only a stand-in for the symbol: handing it to a kernel would fault or touch the wrong memory.)
+static NoAllocScratch* noalloc_scratch_ptr(int* rc) {
+  static std::mutex mu;
+  static NoAllocScratch* ptr[64] = {};
+  int dev = 0;
+  *rc = LGASR_OK;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    *rc = fail(LGASR_ECUDA, "cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      *rc = fail(LGASR_ECUDA, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", dev, cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptr[dev] = static_cast<NoAllocScratch*>(p);
+  }
+  return ptr[dev];
+}
+
+extern "C" int lgasr_row_logsumexp_noalloc(const void* d_logits, int dtype, int64_t ld_in, float* d_lse, int rows, int vocab,
+                                           void* stream) {
+  if (!d_logits || !d_lse || rows < 0 || vocab < 1 || ld_in < vocab || (dtype != LGASR_F32 && dtype != LGASR_BF16))
+    return fail(LGASR_EINVAL, "bad argument");
+  if (rows > kNoAllocMaxRows)
+    return fail(LGASR_EINVAL, "lgasr_row_logsumexp_noalloc: %d rows exceed the fixed scratch (LGASR_NOALLOC_MAX_ROWS = %d)", rows,
+                kNoAllocMaxRows);
+  if (vocab > kNoAllocMaxVocab)
+    return fail(LGASR_EINVAL, "lgasr_row_logsumexp_noalloc: vocabulary %d exceeds LGASR_NOALLOC_MAX_VOCAB = %d", vocab,
+                kNoAllocMaxVocab);
+  if (rows == 0) return LGASR_OK;
+  int rc = LGASR_OK;
+  NoAllocScratch* scr = noalloc_scratch_ptr(&rc);
+  if (!scr) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // slices of at least 8 K entries, at most kNoAllocMaxSplits of them, starting on 32-byte boundaries
+  int nsp = (vocab + 8191) / 8192;
+  if (nsp > kNoAllocMaxSplits) nsp = kNoAllocMaxSplits;
+  if (nsp < 1) nsp = 1;
+  int SL = (vocab + nsp - 1) / nsp;
+  SL = (SL + 7) & ~7;
+  nsp = (vocab + SL - 1) / SL;
+  const bool bf = dtype == LGASR_BF16;
+  const int vq = bf ? 8 : 4;
+  const bool vec = (ld_in % vq) == 0 && ((((uintptr_t)d_logits) & 15) == 0);
+  // the tickets must start at zero whatever an earlier (possibly failed) call left behind; no allocation involved
+  CK(cudaMemsetAsync(&scr->ticket[0], 0, sizeof(int) * (size_t)rows, st));
+  const dim3 grid(nsp, rows);
+  if (bf) {
+    if (vec) k_row_logsumexp_scratch<true, true><<<grid, kNoAllocThreads, 0, st>>>(d_logits, ld_in, d_lse, vocab, SL, scr);
+    else k_row_logsumexp_scratch<true, false><<<grid, kNoAllocThreads, 0, st>>>(d_logits, ld_in, d_lse, vocab, SL, scr);
+  } else {
+    if (vec) k_row_logsumexp_scratch<false, true><<<grid, kNoAllocThreads, 0, st>>>(d_logits, ld_in, d_lse, vocab, SL, scr);
+    else k_row_logsumexp_scratch<false, false><<<grid, kNoAllocThreads, 0, st>>>(d_logits, ld_in, d_lse, vocab, SL, scr);
+  }
+  LAUNCH_CK();
+  return LGASR_OK;
+}
