@@ -27,7 +27,7 @@ def activate() -> None:
     sys.dont_write_bytecode = True
 
 
-def build_search(tables, cfg, device="cpu", lm_tables=None, lm_weight=0.0, row0=0):
+def build_search(tables, cfg, device="cpu", lm_tables=None, lm_weight=0.0, row0=0, ctc_scorer_cls=None):
     """Reference ``BatchBeamSearch`` over table-driven full scorers.
 
     ``tables (L, rows, V)``: the decoder's log-prob matrix of every position (row = running-hypothesis slot, the
@@ -39,6 +39,9 @@ def build_search(tables, cfg, device="cpu", lm_tables=None, lm_weight=0.0, row0=
     from espnet.nets.beam_search import BeamSearch
     from espnet.nets.scorer_interface import BatchScorerInterface
     from espnet.nets.scorers.ctc import CTCPrefixScorer
+
+    if ctc_scorer_cls is not None:  # "scorer only" adoption: the caller's drop-in class under the reference search
+        CTCPrefixScorer = ctc_scorer_cls
     from espnet.nets.scorers.length_bonus import LengthBonus
 
     class SlotTable(BatchScorerInterface):
@@ -79,12 +82,12 @@ def build_search(tables, cfg, device="cpu", lm_tables=None, lm_weight=0.0, row0=
     return bs
 
 
-def decode_one(logp_b, tables_b, cfg, positions, device="cpu", lm_tables_b=None, lm_weight=0.0):
+def decode_one(logp_b, tables_b, cfg, positions, device="cpu", lm_tables_b=None, lm_weight=0.0, ctc_scorer_cls=None):
     """One utterance through the reference search.  Returns ``(seconds, [(tokens, score), ...] n-best)``; the clock
     runs around ``beam_search(x=...)`` only (``time.perf_counter``, with ``cuda.synchronize`` on both sides on a GPU)."""
     import torch
 
-    bs = build_search(tables_b, cfg, device, lm_tables_b, lm_weight)
+    bs = build_search(tables_b, cfg, device, lm_tables_b, lm_weight, ctc_scorer_cls=ctc_scorer_cls)
     x = logp_b.to(device)
     with torch.no_grad():
         if str(device).startswith("cuda"):

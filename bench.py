@@ -278,11 +278,30 @@ def run_reference_gpu(args):
             times.append(dt)
         results.append(nb[0])
     med = statistics.median(times)
+    # "scorer only" adoption (INTEGRATION.md level 1): the same unmodified reference search, our CTCPrefixScorer in it
+    adopt = None
+    try:
+        from llm_guided_asr_b200 import CTCPrefixScorer as OurScorer
+
+        t2, same, maxd = [], True, 0.0
+        for b in utts:
+            dt, nb = rh.decode_one(lp[b], d_tables[:, b * W : (b + 1) * W], cfg, cfg["L"], device=dev, ctc_scorer_cls=OurScorer)
+            if b > 0:
+                t2.append(dt)
+            same = same and nb[0][0] == results[b][0]
+            maxd = max(maxd, abs(nb[0][1] - results[b][1]))
+        m2 = statistics.median(t2)
+        adopt = {"what": "unmodified reference BatchBeamSearch driving llm_guided_asr_b200.CTCPrefixScorer (lgasr_ctc_prefix_score / lgasr_ctc_select_state per call)",
+                 "sec_per_utt_median": m2, "ms_per_position": m2 * 1e3 / cfg["L"], "utts_per_sec": 1.0 / m2,
+                 "speedup_over_reference_scorer": med / m2, "tokens_equal_reference": bool(same), "max_abs_score_diff": maxd}
+    except Exception as e:  # informative
+        adopt = {"unavailable": repr(e)[:200]}
     print(json.dumps({
         "impl": "reference_gpu", "metric": "decode_utts_per_sec", "value": 1.0 / med, "unit": "utts/s",
         "sec_per_utt_median": med, "sec_per_utt_all": times, "ms_per_position": med * 1e3 / cfg["L"],
         "utts": n, "positions": cfg["L"], "device": torch.cuda.get_device_name(0),
         "what": "unmodified reference BatchBeamSearch + CTCPrefixScoreTH on cuda:0 (torch eager fp32), one utterance at a time, table decoder resident on the device",
+        "scorer_only_adoption": adopt,
         "best": [[r[0], r[1]] for r in results],
     }), flush=True)
 

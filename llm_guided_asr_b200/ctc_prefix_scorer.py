@@ -32,6 +32,44 @@ def _st(dev):
     return int(torch.cuda.current_stream(dev).cuda_stream)
 
 
+def _index_vector(vals, dev):
+    """int64 device vector from Python ints or 0-dim tensors (the reference search hands over elements of device
+    tensors, ``batch_beam_search.py:119-128``: they are stacked on the device, never read on the host)."""
+    if all(torch.is_tensor(v) for v in vals):
+        return torch.stack([v.reshape(()) for v in vals]).to(device=dev, dtype=torch.int64)
+    return torch.as_tensor([int(v) for v in vals], dtype=torch.int64, device=dev)
+
+
+class _LazySelect:
+    """Per-hypothesis state handed out by ``CTCPrefixScorer.select_state`` under the reference's search: the batch state
+    it was selected from plus (hypothesis, token).  Reads like the tuple ``(r (2, Tp), log psi, T, (f_min, f_max))``."""
+
+    __slots__ = ("scorer", "impl", "batch", "i", "tok", "value")
+
+    def __init__(self, scorer, batch, i, tok):
+        self.scorer, self.batch, self.i, self.tok, self.value = scorer, batch, i, tok, None
+        self.impl = scorer.impl  # the posteriors the batch state belongs to (extend_prob installs a NEW dict)
+
+    def materialise(self):
+        if self.value is None:
+            r_prev, log_psi, last, olen, _, win, f_now = self.batch
+            dev = r_prev.device
+            hyp = _index_vector([self.i], dev)
+            tok = _index_vector([self.tok], dev)
+            r_new = self.scorer._select(r_prev, last, hyp.to(torch.int32), tok.to(torch.int32), olen, win, impl=self.impl)[0]
+            self.value = (r_new, log_psi[hyp[0], tok[0]], self.impl["T"], f_now)
+        return self.value
+
+    def __getitem__(self, k):
+        return self.materialise()[k]
+
+    def __len__(self):
+        return 4
+
+    def __iter__(self):
+        return iter(self.materialise())
+
+
 class CTCPrefixScorer(BatchPartialScorerInterface):
     """Decoder interface wrapper for the CUDA CTC prefix scorer."""
 
@@ -81,8 +119,9 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
             )
         return scores, log_psi
 
-    def _select(self, r_prev: torch.Tensor, last: torch.Tensor, hyp: torch.Tensor, tok: torch.Tensor, olen: int, win=(0, 0)):
-        m = self.impl
+    def _select(self, r_prev: torch.Tensor, last: torch.Tensor, hyp: torch.Tensor, tok: torch.Tensor, olen: int, win=(0, 0),
+                impl=None):
+        m = self.impl if impl is None else impl
         k = hyp.shape[0]
         r_new = torch.empty(k, 2, m["Tp"], dtype=torch.float32, device=m["device"])
         with torch.cuda.device(m["device"]):
@@ -113,6 +152,18 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         if state is None or state[0] is None:
             r_prev = m["r0"].unsqueeze(0).expand(n, 2, m["Tp"]).contiguous()
             s_prev = torch.zeros(n, dtype=torch.float32, device=dev)
+        elif (all(type(s) is _LazySelect and s.value is None and s.impl is m for s in state)
+              and all(s.batch is state[0].batch for s in state)):
+            # the survivors of ONE earlier call (the reference search's select_state per survivor,
+            # batch_beam_search.py:347-355): one lgasr_ctc_select_state launch and one gather for all of them, the
+            # (hypothesis, token) pairs never visit the host
+            b_r, b_psi, b_last, b_olen, _, b_win, f_prev = state[0].batch
+            hyp = _index_vector([s.i for s in state], dev)
+            tok = _index_vector([s.tok for s in state], dev)
+            r_prev = self._select(b_r, b_last, hyp.to(torch.int32), tok.to(torch.int32), b_olen, b_win)
+            s_prev = b_psi[hyp, tok].to(torch.float32).contiguous()
+            for s_, r_, p_ in zip(state, r_prev, s_prev):  # a later materialise() (streaming, tests) costs nothing
+                s_.value = (r_, p_, m["T"], f_prev)
         else:
             r_prev = torch.stack([s[0] for s in state]).contiguous()
             s_prev = torch.stack([s[1] for s in state]).to(torch.float32).contiguous()
@@ -138,12 +189,9 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         if isinstance(state, list):  # list of per-hypothesis states (batchfy / unbatchfy)
             return state[i]
         if type(state) is tuple and len(state) == 7 and state[4] == "lgasr":  # batch state of this class
-            r_prev, log_psi, last, olen, _, win, f_now = state
-            dev = r_prev.device
-            hyp = torch.as_tensor([int(i)], dtype=torch.int32, device=dev)
-            tok = torch.as_tensor([int(new_id)], dtype=torch.int32, device=dev)
-            r_new = self._select(r_prev, last, hyp, tok, olen, win)[0]
-            return r_new, log_psi[int(i), int(new_id)], self.impl["T"], f_now
+            # lazy: the survivor's state is computed with all its siblings' at the next batch_score_partial, or on
+            # first use as a tuple (r (2, Tp), log psi, T, (f_min, f_max))
+            return _LazySelect(self, state, i, new_id)
         if type(state) is tuple and len(state) == 2 and torch.is_tensor(state[0]) and state[0].dim() > 0:
             # non-batch API: (scores over the candidate ids, states over the candidate ids)
             sc, st = state
@@ -189,7 +237,7 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
             _lib.check(m["lib"].lgasr_transpose_posteriors(logp.data_ptr(), T_new, V, T_new, self.blank, xT.data_ptr(), Tp, _st(dev)))
             xT[:, : m["T"]] = m["xT"][:, : m["T"]]
             _lib.check(m["lib"].lgasr_ctc_initial_state(xT.data_ptr(), T_new, Tp, self.blank, r0.data_ptr(), _st(dev)))
-        m.update(xT=xT, r0=r0, T=T_new, Tp=Tp)
+        self.impl = dict(m, xT=xT, r0=r0, T=T_new, Tp=Tp)  # a new dict: lazy survivor states keep the one they came from
 
     def extend_state(self, state):
         """Per-hypothesis states ``(r (2, Tp_old), s, T_old)`` -> the same states over the extended frames:

@@ -55,3 +55,42 @@ def test_scorer_calls_match_reference(name):
             fin = ref_r[start - 1 :] > -1e9
             np.testing.assert_allclose(r_new[start - 1 :][fin], ref_r[start - 1 :][fin], atol=SCORE_ATOL, rtol=1e-6)
             assert ((r_new[start - 1 :] > -1e9) == fin).all()
+
+
+def test_lazy_survivor_states_equal_materialised_ones():
+    """``select_state`` hands out lazy per-hypothesis states; the next ``batch_score_partial`` computes all survivors in one
+    launch (hypothesis / token indices given as device scalars, the way the reference search passes them).  Same scores,
+    same states as the one-at-a-time path, and a state that was read as a tuple keeps working."""
+    from llm_guided_asr_b200 import CTCPrefixScorer
+    from llm_guided_asr_b200.testing import synthetic as syn
+
+    dev = torch.device("cuda:0")
+    T, V, eos, n = 57, 40, 39, 4
+    g = torch.Generator().manual_seed(3)
+    logp = torch.log_softmax(2.0 * torch.randn(T, V, generator=g), dim=-1).to(dev)
+    sc = CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=eos)
+    sc.batch_init_state(logp)
+    y0 = torch.full((1, 1), eos, dtype=torch.int64, device=dev)
+    ids0 = torch.tensor([[5, 9, 17, 23, eos]], dtype=torch.int64, device=dev)
+    _, bst0 = sc.batch_score_partial(y0, ids0, [None], None)
+    toks = [5, 9, 17, 23]
+    y1 = torch.tensor([[eos, t] for t in toks], dtype=torch.int64, device=dev)
+    ids1 = torch.tensor([[3, 5, 9, 30, eos]] * n, dtype=torch.int64, device=dev)
+    hyp_t = torch.zeros(n, dtype=torch.int64, device=dev)
+    tok_t = torch.tensor(toks, dtype=torch.int64, device=dev)
+    lazy = [sc.select_state(bst0, hyp_t[k], tok_t[k]) for k in range(n)]  # 0-dim device tensors, never read on the host
+    eager = [tuple(sc.select_state(bst0, 0, t)) for t in toks]  # tuple(): materialised one at a time
+    s_lazy, b_lazy = sc.batch_score_partial(y1, ids1, lazy, None)
+    s_eager, b_eager = sc.batch_score_partial(y1, ids1, eager, None)
+    assert torch.equal(s_lazy, s_eager)
+    assert torch.equal(b_lazy[0][..., :T], b_eager[0][..., :T]) and torch.equal(b_lazy[1], b_eager[1])  # (frames >= T: padding)
+    for lz, eg in zip(lazy, eager):  # after the batched call a lazy state reads like the tuple
+        assert torch.equal(lz[0][:, :T], eg[0][:, :T]) and float(lz[1]) == float(eg[1]) and lz[2] == eg[2] == T and len(lz) == 4
+    # one more position from survivors of different parents, mixed with an already materialised state
+    nxt = [sc.select_state(b_lazy, 2, 30), sc.select_state(b_lazy, 0, 3), sc.select_state(b_lazy, 3, 9)]
+    _ = nxt[1][0]
+    y2 = torch.tensor([[eos, 17, 30], [eos, 5, 3], [eos, 23, 9]], dtype=torch.int64, device=dev)
+    s_mixed, _ = sc.batch_score_partial(y2, ids1[:3], nxt, None)
+    ref = [tuple(sc.select_state(b_eager, h, t)) for h, t in ((2, 30), (0, 3), (3, 9))]
+    s_ref, _ = sc.batch_score_partial(y2, ids1[:3], ref, None)
+    assert torch.equal(s_mixed, s_ref)
