@@ -71,6 +71,10 @@ def row_logsumexp(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> t
     return out
 
 
+class _InPlaceCaches(list):
+    """Per-layer caches that are views ``[:, :L]`` of the scorer's current persistent buffer (appended in place)."""
+
+
 class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
     """Machinery shared by the device-protocol scorers: static buffers per batch shape, one network call per
     position for all ``B*beam`` row slots (``_net``), ``lgasr_log_softmax_rows`` into the row layout of
@@ -94,6 +98,7 @@ class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
         self._shape = None
         self._graphs = {}
         self._pool = None
+        self._slots, self._inplace = None, False
 
     # ---- plain scorer protocol: delegate to the wrapped network --------------------------------------------
     def batch_init_state(self, x):
@@ -150,11 +155,18 @@ class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
         per-layer caches ``(B*W, L, Dm)``."""
         tgt = self._tgt[:, :L]
         nl = self._n_layers()
+        self._slots = None
         if self._fresh or self._buf is None or L == 1:
             cache = [None] * nl
         else:
             cache = [self._buf[self._pp][i, :, : L - 1] for i in range(nl)]
+            # where a network can append its new cache entry in place (position L - 1 of the persistent buffer it reads
+            # the earlier positions from) instead of returning a concatenated copy
+            self._slots = [self._buf[self._pp][i, :, :L] for i in range(nl)]
+        self._inplace = False
         logits, new = self._net(tgt, cache)
+        if self._inplace:
+            new = _InPlaceCaches(new)
         if logits.dtype not in (torch.float32, torch.bfloat16):
             logits = logits.float()
         if self._out is None:  # fused normaliser: (logits, logsumexp) go to the step as they are
@@ -212,8 +224,11 @@ class _DeviceCachedScorer(torch.nn.Module, BatchScorerInterface):
             nl, BW = len(new), new[0].shape[0]
             self._buf = [torch.zeros(nl, BW, self._cap, Dm, dtype=new[0].dtype, device=new[0].device) for _ in range(2)]
         dst = self._buf[self._pp ^ 1]
-        for i, src in enumerate(new):
-            self._eng.reorder_rows(dst[i], src.contiguous(), row_elems=L * Dm)
+        if isinstance(new, _InPlaceCaches):  # the caches are views of the current buffer: ONE gather for all layers
+            self._eng.reorder_rows(dst, self._buf[self._pp][:, :, :L], row_elems=L * Dm)
+        else:
+            for i, src in enumerate(new):
+                self._eng.reorder_rows(dst[i], src.contiguous(), row_elems=L * Dm)
         self._pp ^= 1
         self._new = None
         self._fresh = False
@@ -288,7 +303,7 @@ class DeviceCachedDecoderScorer(_DeviceCachedScorer):
             mem[b, :, : lens[b]] = x
         self._memory_mask.view(B, W, T).copy_(mask[:, None, :].expand(B, W, T))
 
-    def _layer_fast(self, layer, x, cache, kT, v, tgt_mask):
+    def _layer_fast(self, layer, x, cache, kT, v, tgt_mask, slot=None):
         """One reference ``DecoderLayer`` (``decoder_layer.py:73-150``), same arithmetic per row, with two caches the
         reference does not keep: the memory keys / values of the utterance (``kT``, ``v``; shared by its ``beam`` rows)
         and the layer's own self-attention keys / values of the earlier positions (``cache (n, L-1, 2D)``; the reference
@@ -303,7 +318,13 @@ class DeviceCachedDecoderScorer(_DeviceCachedScorer):
         residual = x
         t = layer.norm1(x) if nb else x
         kv_new = torch.cat([sa.linear_k(t), sa.linear_v(t)], dim=-1)  # (n, Lq, 2D)
-        kv = kv_new if cache is None else torch.cat([cache, kv_new], dim=1)
+        if cache is None:
+            kv = kv_new
+        elif slot is not None:  # append in place: slot (n, L, 2D) is the persistent buffer the cache is a view of
+            slot[:, -1:].copy_(kv_new)
+            kv = slot
+        else:
+            kv = torch.cat([cache, kv_new], dim=1)
         L = kv.shape[1]
         q = sa.linear_q(t).view(n, Lq, H, dk).transpose(1, 2)
         k = kv[..., :D].reshape(n, L, H, dk).transpose(1, 2)
@@ -346,9 +367,11 @@ class DeviceCachedDecoderScorer(_DeviceCachedScorer):
         if self._fast:
             if cache[0] is not None:
                 x = x[:, -1:]  # earlier positions live in the key / value caches
-            for c, layer, (kT, v) in zip(cache, dec.decoders, self._mem_kv):
-                x, kv = self._layer_fast(layer, x, c, kT, v, tgt_mask)
+            slots = self._slots if (self._slots is not None and cache[0] is not None) else [None] * len(cache)
+            for c, layer, (kT, v), sl in zip(cache, dec.decoders, self._mem_kv, slots):
+                x, kv = self._layer_fast(layer, x, c, kT, v, tgt_mask, sl)
                 new.append(kv)
+            self._inplace = slots[0] is not None
         else:
             memory, memory_mask = self._memory, self._memory_mask
             for c, layer in zip(cache, dec.decoders):
