@@ -54,6 +54,21 @@ def length_bounds(T: int, maxlenratio: float, minlenratio: float):
     return maxlen, minlen
 
 
+def _auto_device_cache(v):
+    """Device-protocol wrapper for a full scorer with the reference's ``BaseTransformerDecoder`` or ``TransformerLM``
+    surface, None for anything else (scorers that already speak the device protocol, table scorers, the LLM-guided
+    decoder and HF language models, which the caller wraps explicitly: their prompts / tokenizers need arguments)."""
+    if hasattr(v, "batch_score_padded") or not isinstance(v, torch.nn.Module) or hasattr(v, "llm"):
+        return None
+    from .device_cache import DeviceCachedDecoderScorer, DeviceCachedLMScorer
+
+    if all(hasattr(v, a) for a in ("embed", "decoders", "output_layer", "forward_one_step")):
+        return DeviceCachedDecoderScorer(v)
+    if all(hasattr(v, a) for a in ("embed", "encoder", "decoder")) and hasattr(v.encoder, "encoders"):
+        return DeviceCachedLMScorer(v)
+    return None
+
+
 class BatchBeamSearch(torch.nn.Module):
     """Fused batch beam search (one or many utterances in lock-step)."""
 
@@ -71,6 +86,7 @@ class BatchBeamSearch(torch.nn.Module):
         return_hs: bool = False,
         hyp_primer: List[int] = None,
         normalize_length: bool = False,
+        device_caches: bool = True,
     ):
         super().__init__()
         self.weights = weights
@@ -93,6 +109,17 @@ class BatchBeamSearch(torch.nn.Module):
         for k, v in self.full_scorers.items():
             if not isinstance(v, BatchScorerInterface):
                 raise NotImplementedError(f"full scorer {k} is not a BatchScorerInterface (asr_inference.py:365-380)")
+        if device_caches:
+            # the reference's own attention decoder / TransformerLM handed over as they are (the plain class swap of
+            # INTEGRATION.md): wrap them so that decode_batch calls them once per position for all row slots and keeps
+            # their caches on the device, instead of one batch_score per utterance with per-hypothesis state lists
+            # (batch_beam_search.py:347-355, transformer_decoder.py:268-272,285-286).  device_caches=False keeps
+            # the generic protocol.
+            for k, v in list(self.full_scorers.items()):
+                w = _auto_device_cache(v)
+                if w is not None:
+                    self.full_scorers[k] = self.scorers[k] = w
+                    self.nn_dict[k] = w
         if len(self.part_scorers) > 1 or any(not hasattr(v, "ctc") for v in self.part_scorers.values()):
             raise NotImplementedError("the fused step supports exactly one partial scorer: the CTC prefix scorer")
         if return_hs:

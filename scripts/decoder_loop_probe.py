@@ -37,7 +37,7 @@ def main(B=8, T=374, V=5000, D=256, layers=6, beam=10, L=32):
     weights = dict(decoder=0.7, ctc=0.3, length_bonus=0.1)
 
     def search(scorer):
-        return BatchBeamSearch(scorers=dict(decoder=scorer, ctc=CTCPrefixScorer(ctc=ctc, eos=eos), length_bonus=LengthBonus(V)),
+        return BatchBeamSearch(device_caches=False, scorers=dict(decoder=scorer, ctc=CTCPrefixScorer(ctc=ctc, eos=eos), length_bonus=LengthBonus(V)),
                                weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
 
     out = {}

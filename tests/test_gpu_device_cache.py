@@ -138,13 +138,18 @@ def test_device_cached_decoder_decode(fused_lsm):
     dec, ctc = syn.TinyDecoder(V, D=D, seed=2).eval().to(DEV), ProjCTC().eval().to(DEV)
     weights = dict(decoder=0.7, ctc=0.3, length_bonus=0.3)
 
-    def search(decoder_scorer):
+    def search(decoder_scorer, **kw):
         return BatchBeamSearch(scorers=dict(decoder=decoder_scorer, ctc=CTCPrefixScorer(ctc=ctc, eos=eos), length_bonus=LengthBonus(V)),
-                               weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
+                               weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full", **kw)
 
     xs = [e.to(DEV) for e in encs]
     got = search(DeviceCachedDecoderScorer(dec, fused_log_softmax=fused_lsm)).decode_batch(xs, -14, 0.0)
-    host = search(dec).decode_batch(xs, -14, 0.0)  # per-hypothesis host states (the reference's protocol)
+    host = search(dec, device_caches=False).decode_batch(xs, -14, 0.0)  # per-hypothesis host states (the reference's protocol)
+    auto = search(dec)  # the bare decoder handed over as it is: wrapped by the search itself
+    assert isinstance(auto.full_scorers["decoder"], DeviceCachedDecoderScorer) and auto.nn_dict["decoder"].net is dec
+    for u, v in zip(auto.decode_batch(xs, -14, 0.0), got):
+        assert [h.yseq.tolist() for h in u] == [h.yseq.tolist() for h in v]
+        assert all(abs(float(a.score) - float(b.score)) <= SCORE_ATOL for a, b in zip(u, v))
     for b in range(len(lens)):
         assert len(got[b]) == len(host[b]) >= 1
         for h, r in zip(got[b], host[b]):
@@ -209,12 +214,13 @@ def test_device_cached_decoder_and_lm_together(graphs):
     lm = syn.TinyLM(V, seed=9).eval().to(DEV)
     weights = dict(decoder=0.6, ctc=0.4, lm=0.5)
 
-    def search(d, m):
+    def search(d, m, **kw):
         return BatchBeamSearch(scorers=dict(decoder=d, ctc=CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=eos), lm=m),
-                               weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
+                               weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full", **kw)
 
     dev_bs = search(DeviceCachedDecoderScorer(dec, cuda_graphs=graphs), DeviceCachedLMScorer(lm, cuda_graphs=graphs))
-    host_bs = search(dec, lm)
+    host_bs = search(dec, lm, device_caches=False)
+    assert isinstance(search(dec, lm).full_scorers["lm"], DeviceCachedLMScorer)  # bare TransformerLM surface: wrapped too
     for batch in range(2):
         lens = [26, 33, 19]
         xs = [syn.random_logp(200 + 10 * batch + i, t, V, scale=2.0).to(DEV) for i, t in enumerate(lens)]

@@ -165,13 +165,13 @@ def test_reference_transformer_decoder_under_device_protocol(graphs):
     xs = [torch.randn(T, D, generator=g).to(DEV) for T in (33, 27, 33)]
     weights = dict(decoder=0.7, ctc=0.3, length_bonus=0.2)
 
-    def run(scorer, batch):
+    def run(scorer, batch, **kw):
         bs = BatchBeamSearch(scorers=dict(decoder=scorer, ctc=CTCPrefixScorer(ctc=ctc, eos=eos), length_bonus=LengthBonus(V)),
-                             weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
+                             weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full", **kw)
         with torch.no_grad():
             return bs.decode_batch(batch, -10, 0.0)
 
-    plain = [run(dec, [x])[0] for x in xs]
+    plain = [run(dec, [x], device_caches=False)[0] for x in xs]  # the reference's own batch_score / state-list protocol
     wrapped = DeviceCachedDecoderScorer(dec, cuda_graphs=graphs)
     for rep in range(2):  # the second batch replays the captured graphs
         both = run(wrapped, xs)
