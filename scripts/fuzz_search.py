@@ -92,11 +92,61 @@ def run(n, seed0):
     return bad
 
 
+def run_batched(n, seed0):
+    """decode_batch over 2-6 utterances of different lengths (lock-step, ragged) and decode_stream (continuous batching)
+    against one-utterance decodes of the same search object: identical n-best lists, bit for bit."""
+    import numpy as np
+    import torch
+
+    from llm_guided_asr_b200 import BatchBeamSearch, CTCPrefixScorer, LengthBonus
+    from llm_guided_asr_b200.testing import synthetic as syn
+
+    dev = torch.device("cuda:0")
+    bad = 0
+    for case in range(n):
+        rng = np.random.default_rng(seed0 + case)
+        V = int(rng.choice([13, 30, 101, 600]))
+        beam = int(rng.integers(1, 7))
+        K = int(rng.integers(1, 3))
+        eos = V - 1
+        nu = int(rng.integers(2, 7))
+        lens = [int(v) for v in rng.integers(4, 70, size=nu)]
+        names = ["decoder", "lm"][:K]
+        tabs = [syn.random_table(seed0 * 3 + case + k, max(lens) + 2, 3, V, scale=1.5) for k in range(K)]
+        xs = [syn.peaky_case(seed0 * 5 + case * 7 + u, t, V, max(1, min(8, t // 3)), eos)[0].to(dev) for u, t in enumerate(lens)]
+        weights = {nm: float(rng.choice([0.3, 0.7])) for nm in names}
+        weights["ctc"] = float(rng.choice([0.3, 0.5]))
+        weights["length_bonus"] = float(rng.choice([0.0, 0.3]))
+        maxr = float(rng.choice([0.0, 0.0, -6.0]))
+        scorers = {nm: syn.PrefixTableScorer(t.to(dev)) for nm, t in zip(names, tabs)}
+        scorers["ctc"] = CTCPrefixScorer(ctc=syn.IdentityCTC(), eos=eos)
+        scorers["length_bonus"] = LengthBonus(V)
+        bs = BatchBeamSearch(scorers=scorers, weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos, pre_beam_score_key="full")
+        desc = dict(case=seed0 + case, V=V, beam=beam, K=K, lens=lens, w=weights, maxr=maxr)
+        try:
+            single = [bs(x, maxr, 0.0) for x in xs]
+            both = bs.decode_batch(xs, maxr, 0.0)
+            stream = bs.decode_stream(xs, slots=int(rng.integers(1, nu + 1)), maxlenratio=maxr, minlenratio=0.0)
+            ok = True
+            for a, b, c in zip(single, both, stream):
+                for other in (b, c):
+                    ok = ok and len(a) == len(other) and all(
+                        h.yseq.tolist() == g.yseq.tolist() and float(h.score) == float(g.score) for h, g in zip(a, other))
+        except Exception as e:
+            ok = False
+            desc["error"] = repr(e)[:200]
+        if not ok:
+            bad += 1
+            print("BATCH MISMATCH", desc, flush=True)
+    print(f"{n} batched cases, {bad} mismatches (env V2={os.environ.get('LGASR_V2')} NO_CLUSTER={os.environ.get('LGASR_NO_CLUSTER')})", flush=True)
+    return bad
+
+
 if __name__ == "__main__":
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 60
     seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1000
     if os.environ.get("FUZZ_CHILD"):
-        sys.exit(1 if run(n, seed0) else 0)
+        sys.exit(1 if (run(n, seed0) + run_batched(max(1, n // 4), seed0)) else 0)
     rc = 0
     for env in ({}, {"LGASR_V2": "1"}, {"LGASR_NO_CLUSTER": "1"}):
         e = dict(os.environ, FUZZ_CHILD="1", **env)

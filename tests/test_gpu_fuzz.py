@@ -20,3 +20,4 @@ def test_random_configurations_match_the_oracle(monkeypatch, env):
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     assert fuzz_search.run(40, 5000) == 0
+    assert fuzz_search.run_batched(10, 6000) == 0  # decode_batch / decode_stream == one-utterance decodes, bit for bit
