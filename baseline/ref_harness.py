@@ -82,6 +82,30 @@ def build_search(tables, cfg, device="cpu", lm_tables=None, lm_weight=0.0, row0=
     return bs
 
 
+def table_parts(tables, device="cpu", row0=0):
+    """The two stand-ins of ``build_search`` on their own (for a search object built by the caller): a table-driven full
+    scorer (``BatchScorerInterface`` of the reference) and the identity CTC head."""
+    activate()
+    import torch
+    from espnet.nets.scorer_interface import BatchScorerInterface
+
+    t = tables.to(device)
+
+    class SlotTable(BatchScorerInterface):
+        def score(self, y, state, x):
+            return t[y.shape[0] - 1, row0], None
+
+        def batch_score(self, ys, states, xs):
+            n = ys.shape[0]
+            return t[ys.shape[1] - 1, row0 : row0 + n], [None] * n
+
+    class IdentityCTC(torch.nn.Module):
+        def log_softmax(self, hs_pad):
+            return hs_pad.clone()
+
+    return SlotTable(), IdentityCTC()
+
+
 def decode_one(logp_b, tables_b, cfg, positions, device="cpu", lm_tables_b=None, lm_weight=0.0, ctc_scorer_cls=None):
     """One utterance through the reference search.  Returns ``(seconds, [(tokens, score), ...] n-best)``; the clock
     runs around ``beam_search(x=...)`` only (``time.perf_counter``, with ``cuda.synchronize`` on both sides on a GPU)."""

@@ -296,12 +296,44 @@ def run_reference_gpu(args):
                  "speedup_over_reference_scorer": med / m2, "tokens_equal_reference": bool(same), "max_abs_score_diff": maxd}
     except Exception as e:  # informative
         adopt = {"unavailable": repr(e)[:200]}
+    # the reference's own operating point, one utterance at a time (asr_inference.py:759-764), through OUR search:
+    # BatchBeamSearch.forward(x) = one lgasr_step + one poll per position, the same table scorer and inputs
+    single = None
+    try:
+        from llm_guided_asr_b200 import BatchBeamSearch as OurSearch
+        from llm_guided_asr_b200 import CTCPrefixScorer as OurScorer
+
+        t3, same, maxd = [], True, 0.0
+        eos = cfg["V"] - 1
+        for b in utts:
+            tab, ident = rh.table_parts(d_tables[:, b * W : (b + 1) * W], dev)
+            bs = OurSearch(scorers=dict(decoder=tab, ctc=OurScorer(ctc=ident, eos=eos)),
+                           weights=dict(decoder=1.0 - cfg["ctc_weight"], ctc=cfg["ctc_weight"]), beam_size=W, vocab_size=cfg["V"],
+                           sos=eos, eos=eos, pre_beam_score_key="full")
+            x = lp[b].to(dev)
+            with torch.no_grad():
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                nb = bs(x, -float(cfg["L"]), 0.0)
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+            if b > 0:
+                t3.append(dt)
+            same = same and [int(v) for v in nb[0].yseq.tolist()] == results[b][0]
+            maxd = max(maxd, abs(float(nb[0].score) - results[b][1]))
+        m3 = statistics.median(t3)
+        single = {"what": "llm_guided_asr_b200.BatchBeamSearch.forward, one utterance at a time (new search object per utterance, as the reference arm), same table scorer",
+                  "sec_per_utt_median": m3, "ms_per_position": m3 * 1e3 / cfg["L"], "utts_per_sec": 1.0 / m3,
+                  "speedup_over_reference_gpu": med / m3, "tokens_equal_reference": bool(same), "max_abs_score_diff": maxd}
+    except Exception as e:  # informative
+        single = {"unavailable": repr(e)[:200]}
     print(json.dumps({
         "impl": "reference_gpu", "metric": "decode_utts_per_sec", "value": 1.0 / med, "unit": "utts/s",
         "sec_per_utt_median": med, "sec_per_utt_all": times, "ms_per_position": med * 1e3 / cfg["L"],
         "utts": n, "positions": cfg["L"], "device": torch.cuda.get_device_name(0),
         "what": "unmodified reference BatchBeamSearch + CTCPrefixScoreTH on cuda:0 (torch eager fp32), one utterance at a time, table decoder resident on the device",
         "scorer_only_adoption": adopt,
+        "fused_search_single_utterance": single,
         "best": [[r[0], r[1]] for r in results],
     }), flush=True)
 
