@@ -595,6 +595,8 @@ def run_decode_real(dev, cfg, reps=3):
                     if it and not bs.collect_timing:
                         best = min(best, time.perf_counter() - t0)
             tm = bs.last_timing
+            if name == "fp32":
+                fp32_res = res
             out[name] = {
                 "ms_per_batch": best * 1e3, "utts_per_sec": B / best, "ms_per_position": best * 1e3 / bs.last_steps,
                 "positions_run": bs.last_steps, "hyps_first_utt": len(res[0]),
@@ -604,6 +606,41 @@ def run_decode_real(dev, cfg, reps=3):
         finally:
             torch.backends.cuda.matmul.allow_tf32 = old_tf32
         torch.cuda.empty_cache()
+    # the unmodified reference on the same GPU with the SAME decoder and CTC head, one utterance at a time (its operating
+    # point): reference BatchBeamSearch + CTCPrefixScorer + TransformerDecoder.batch_score, eager fp32
+    if rh.available() and kind.startswith("reference"):
+        try:
+            _quiet_reference_logs()
+            from espnet.nets.batch_beam_search import BatchBeamSearch as RefBBS
+            from espnet.nets.beam_search import BeamSearch as RefBS
+            from espnet.nets.scorers.ctc import CTCPrefixScorer as RefCTC
+
+            rbs = RefBS(beam_size=W, weights=dict(decoder=1.0 - cfg["ctc_weight"], ctc=cfg["ctc_weight"]),
+                        scorers=dict(decoder=dec, ctc=RefCTC(ctc=ctc, eos=eos)), sos=eos, eos=eos, vocab_size=V, token_list=None,
+                        pre_beam_score_key="full")
+            rbs.__class__ = RefBBS
+            rbs.to(device=dev, dtype=torch.float32).eval()
+            times, same, maxd = [], True, 0.0
+            with torch.no_grad():
+                for u in range(3):  # utterance 0 is the warm-up
+                    torch.cuda.synchronize(dev)
+                    t0 = time.perf_counter()
+                    nb = rbs(x=xs[u], maxlenratio=-float(L), minlenratio=0.0)
+                    torch.cuda.synchronize(dev)
+                    if u:
+                        times.append(time.perf_counter() - t0)
+                    ours = fp32_res[u][0]
+                    same = same and [int(v) for v in nb[0].yseq.tolist()] == [int(v) for v in ours.yseq.tolist()]
+                    maxd = max(maxd, abs(float(nb[0].score) - float(ours.score)))
+            sec = statistics.median(times)
+            out["reference_gpu_same_decoder"] = {
+                "what": "unmodified reference BatchBeamSearch + CTCPrefixScorer + TransformerDecoder.batch_score on cuda:0, one utterance at a time, eager fp32",
+                "sec_per_utt": sec, "ms_per_position": sec * 1e3 / L, "utts_per_sec": 1.0 / sec,
+                "ours_fp32_over_reference": out["fp32"]["utts_per_sec"] * sec,
+                "best_tokens_equal_ours_fp32": bool(same), "max_abs_best_score_diff": maxd,
+            }
+        except Exception as e:  # informative
+            out["reference_gpu_same_decoder"] = {"unavailable": repr(e)[:300]}
     return out
 
 
