@@ -1475,7 +1475,7 @@ __device__ __forceinline__ void lse_merge(float& m, float& s, float m2, float s2
   // (m, s) (+) (m2, s2) with s = sum exp(x - m); an empty side has m = -inf, s = 0
   const float mm = fmaxf(m, m2);
   if (mm == -INFINITY) return;
-  s = s * expf(m - mm) + s2 * expf(m2 - mm);
+  s = s * exp2f((m - mm) * 1.4426950408889634f) + s2 * exp2f((m2 - mm) * 1.4426950408889634f);
   m = mm;
 }
 
@@ -1489,27 +1489,38 @@ __global__ void __launch_bounds__(kNoAllocThreads) k_row_logsumexp_scratch(const
   const int e0 = sp * SL;
   const int e1 = min(V, e0 + SL);
   float m = -INFINITY, s = 0.f;
+  constexpr float kL2E = 1.4426950408889634f;
+  // online (max, sum): s = sum of 2^((x - m) * log2 e) relative to the running maximum m (MUFU ex2, as the staged kernel)
   auto take = [&](float x) {
     if (x > m) {
-      s = s * expf(m - x) + 1.f;  // expf(-inf) = 0 on the first element
+      s = s * ex2_approx((m - x) * kL2E) + 1.f;  // 2^(-inf) = 0 on the first element
       m = x;
     } else if (x > -INFINITY) {
-      s += expf(x - m);
+      s += ex2_approx((x - m) * kL2E);
     }
+  };
+  // four values at once: one maximum update (rare after the first few vectors), then four independent exponentials
+  auto take4 = [&](float a, float b, float c, float d4) {
+    const float mv = fmaxf(fmaxf(a, b), fmaxf(c, d4));
+    if (mv > m) {
+      s *= ex2_approx((m - mv) * kL2E);
+      m = mv;
+    }
+    if (m > -INFINITY)
+      s += (ex2_approx((a - m) * kL2E) + ex2_approx((b - m) * kL2E)) + (ex2_approx((c - m) * kL2E) + ex2_approx((d4 - m) * kL2E));
   };
   if (BF16) {
     const __nv_bfloat16* row = reinterpret_cast<const __nv_bfloat16*>(logits) + (long long)r * ld_in;
     if (VEC) {  // SL % 8 == 0, 16-byte aligned rows
       const uint4* p = reinterpret_cast<const uint4*>(row + e0);
       const int nq = (e1 - e0) >> 3;
+#pragma unroll 2
       for (int q = tid; q < nq; q += kNoAllocThreads) {
         const uint4 u = __ldg(p + q);
-        const unsigned w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          take(__uint_as_float(w[k] << 16));
-          take(__uint_as_float(w[k] & 0xffff0000u));
-        }
+        take4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u), __uint_as_float(u.y << 16),
+              __uint_as_float(u.y & 0xffff0000u));
+        take4(__uint_as_float(u.z << 16), __uint_as_float(u.z & 0xffff0000u), __uint_as_float(u.w << 16),
+              __uint_as_float(u.w & 0xffff0000u));
       }
       for (int e = e0 + (nq << 3) + tid; e < e1; e += kNoAllocThreads) take(__bfloat162float(row[e]));
     } else {
@@ -1520,12 +1531,10 @@ __global__ void __launch_bounds__(kNoAllocThreads) k_row_logsumexp_scratch(const
     if (VEC) {
       const float4* p = reinterpret_cast<const float4*>(row + e0);
       const int nq = (e1 - e0) >> 2;
+#pragma unroll 2
       for (int q = tid; q < nq; q += kNoAllocThreads) {
         const float4 v = __ldg(p + q);
-        take(v.x);
-        take(v.y);
-        take(v.z);
-        take(v.w);
+        take4(v.x, v.y, v.z, v.w);
       }
       for (int e = e0 + (nq << 2) + tid; e < e1; e += kNoAllocThreads) take(__ldg(row + e));
     } else {
